@@ -20,6 +20,7 @@ import numpy as np
 OPTIMAL = "optimal"
 OPTIMAL_INACCURATE = "optimal_inaccurate"
 INFEASIBLE = "infeasible"
+VERBOSE = False
 
 
 def _kkt_solve(P, E, G, w, r1, r2):
@@ -80,8 +81,118 @@ def polish(P, q, E, e, G, h, z, y, lam, act_tol=1e-6):
     return z, y, lam, False
 
 
-def solve_qp(P, q, E, e, G, h, tol=1e-11, max_iter=100, do_polish=True):
-    """Returns dict(z, y, lam, s, status, iters, polished)."""
+def _ipm_ineq(H, g, G, h, tol, max_iter):
+    """Mehrotra predictor-corrector for min 1/2 w'Hw + g'w s.t. Gw <= h (H SPD), Cholesky normal equations.
+
+    Runs until the scaled KKT merit max(|rd|/gscale, |rp|, mu) < tol or stops improving, and returns the
+    best iterate seen; the caller's active-set polish then removes the remaining O(sqrt(mu)) error.
+    """
+    n = H.shape[0]
+    m = G.shape[0]
+    if m == 0:
+        w = np.linalg.solve(H, -g)
+        return w, np.zeros(0), np.zeros(0), OPTIMAL, 0
+    # well-centred start: unit duals, slacks at least 1 (an infeasible-start method; rp absorbs the rest)
+    w = np.linalg.solve(H + G.T @ G, -g + G.T @ h)
+    s = np.maximum(h - G @ w, 1.0)
+    lam = np.ones(m)
+    gscale = 1.0 + np.abs(g).max(initial=0.0)
+    best = None
+    stall = 0
+    it = 0
+    for it in range(1, max_iter + 1):
+        rd = H @ w + g + G.T @ lam
+        rp = G @ w + s - h
+        mu = float(s @ lam) / m
+        merit = max(np.abs(rd).max() / gscale, np.abs(rp).max(), mu)
+        if VERBOSE:
+            print("ipm", it, np.abs(rd).max(), np.abs(rp).max(), mu)
+        if best is None or merit < best[0]:
+            best = (merit, w.copy(), s.copy(), lam.copy(), it)
+            stall = 0
+        else:
+            stall += 1
+        if merit < tol or stall >= 15 or mu < 1e-15:
+            break
+        ws = lam / s
+        M = H + G.T @ (ws[:, None] * G)
+        try:
+            Lc = np.linalg.cholesky(M)
+        except np.linalg.LinAlgError:
+            break
+
+        def direction(rc):
+            rhs = -rd + G.T @ (rc / s - ws * rp)
+            dw = np.linalg.solve(Lc.T, np.linalg.solve(Lc, rhs))
+            res = rhs - M @ dw                      # one step of iterative refinement
+            dw = dw + np.linalg.solve(Lc.T, np.linalg.solve(Lc, res))
+            ds = -rp - G @ dw
+            dl = -(rc + lam * ds) / s
+            return dw, ds, dl
+
+        def max_step(v, dv):
+            neg = dv < 0
+            return min(1.0, float((-v[neg] / dv[neg]).min())) if neg.any() else 1.0
+
+        dw_a, ds_a, dl_a = direction(s * lam)
+        a_aff = min(max_step(s, ds_a), max_step(lam, dl_a))
+        mu_aff = float((s + a_aff * ds_a) @ (lam + a_aff * dl_a)) / m
+        sigma = (mu_aff / mu) ** 3 if mu > 0 else 0.0
+        dw, ds, dl = direction(s * lam + ds_a * dl_a - sigma * mu)
+        a = min(1.0, 0.99 * min(max_step(s, ds), max_step(lam, dl)))
+        w, s, lam = w + a * dw, s + a * ds, lam + a * dl
+        if not np.isfinite(w).all() or np.abs(w).max(initial=0.0) > 1e12:
+            return w, s, lam, INFEASIBLE, it
+    merit, w, s, lam, _ = best
+    if merit < 1e-8:
+        status = OPTIMAL
+    elif merit < 1e-5:
+        status = OPTIMAL_INACCURATE
+    else:
+        status = INFEASIBLE
+    return w, s, lam, status, it
+
+
+def _polish_ineq(H, g, G, h, w, lam):
+    """Active-set refinement on the reduced problem; dependent active rows are dropped by pivoted QR."""
+    import scipy.linalg as sla
+    slack = h - G @ w
+    active = np.where(lam > slack)[0]
+    n = H.shape[0]
+    if len(active):
+        Ga = G[active]
+        _, R, piv = sla.qr(Ga.T, mode="economic", pivoting=True)
+        diag = np.abs(np.diag(R))
+        rank = int((diag > 1e-9 * max(diag.max(initial=0.0), 1e-300)).sum())
+        active = active[np.sort(piv[:rank])]
+    Ga = G[active]
+    k = len(active)
+    K = np.zeros((n + k, n + k))
+    K[:n, :n] = H
+    K[:n, n:] = Ga.T
+    K[n:, :n] = Ga
+    try:
+        sol = np.linalg.solve(K, np.concatenate([-g, h[active]]))
+        res = np.concatenate([-g, h[active]]) - K @ sol
+        sol = sol + np.linalg.solve(K, res)
+    except np.linalg.LinAlgError:
+        return w, lam, False
+    w2 = sol[:n]
+    lam2 = np.zeros_like(lam)
+    lam2[active] = sol[n:]
+    viol = max(0.0, float((G @ w2 - h).max(initial=0.0)))
+    if viol < 1e-9 and lam2.min(initial=0.0) > -1e-7 * (1.0 + np.abs(lam2).max(initial=0.0)):
+        return w2, lam2, True
+    return w, lam, False
+
+
+def solve_qp(P, q, E, e, G, h, tol=1e-11, max_iter=120, do_polish=True):
+    """Null-space elimination of Ez = e, then an inequality-only IPM on the reduced QP.
+
+    Returns dict(z, y, lam, s, status, iters, polished); lam is for the rows of G (dropped
+    constant rows get 0), y is not recovered (None).
+    """
+    import scipy.linalg as sla
     P = np.asarray(P, float)
     q = np.asarray(q, float)
     n = P.shape[0]
@@ -89,70 +200,31 @@ def solve_qp(P, q, E, e, G, h, tol=1e-11, max_iter=100, do_polish=True):
     e = np.zeros(0) if e is None else np.asarray(e, float).ravel()
     G = np.asarray(G, float).reshape(-1, n)
     h = np.asarray(h, float).ravel()
-    m = G.shape[0]
-
-    # Mehrotra-style starting point
-    z, y = _kkt_solve(P, E, G, np.ones(m), -q + G.T @ h, e)
-    s = h - G @ z
-    lam = np.ones(m)
-    shift = max(0.0, -1.5 * s.min(initial=1.0))
-    s = s + shift
-    s = np.maximum(s, 1e-2)
-
-    status = OPTIMAL_INACCURATE
-    it = 0
-    scale = 1.0 + max(np.abs(q).max(initial=0.0), np.abs(h).max(initial=0.0))
-    for it in range(1, max_iter + 1):
-        rd = P @ z + q + G.T @ lam + (E.T @ y if len(e) else 0.0)
-        rpe = (E @ z - e) if len(e) else np.zeros(0)
-        rpi = G @ z + s - h
-        mu = float(s @ lam) / m
-        res = max(np.abs(rd).max(initial=0.0), np.abs(rpe).max(initial=0.0),
-                  np.abs(rpi).max(initial=0.0))
-        if res < tol * scale and mu < tol:
-            status = OPTIMAL
-            break
-        w = lam / s
-
-        def direction(rc):
-            # rc = target for s*lam residual (vector)
-            r1 = -rd + G.T @ (rc / s - w * rpi)
-            dz, dy = _kkt_solve(P, E, G, w, r1, -rpe)
-            ds = -rpi - G @ dz
-            dlam = -(rc + lam * ds) / s
-            return dz, dy, ds, dlam
-
-        def max_step(v, dv):
-            neg = dv < 0
-            if not neg.any():
-                return 1.0
-            return min(1.0, float((-v[neg] / dv[neg]).min()))
-
-        dz_a, dy_a, ds_a, dl_a = direction(s * lam)
-        a_aff = min(max_step(s, ds_a), max_step(lam, dl_a))
-        mu_aff = float((s + a_aff * ds_a) @ (lam + a_aff * dl_a)) / m
-        sigma = (mu_aff / mu) ** 3 if mu > 0 else 0.0
-        rc = s * lam + ds_a * dl_a - sigma * mu
-        dz, dy, ds, dl = direction(rc)
-        a = 0.995 * min(max_step(s, ds), max_step(lam, dl))
-        a = min(a, 1.0)
-        z = z + a * dz
-        y = y + a * dy
-        s = s + a * ds
-        lam = lam + a * dl
-        if not np.isfinite(z).all() or np.abs(z).max(initial=0.0) > 1e12:
-            status = INFEASIBLE
-            break
+    if E.shape[0]:
+        Q, R = sla.qr(E.T, mode="full")               # E' = Q R
+        p = E.shape[0]
+        R1 = R[:p, :]
+        zp = Q[:, :p] @ sla.solve_triangular(R1, e, trans="T")   # particular solution
+        N = Q[:, p:]
     else:
-        # ran out of iterations
-        rd = P @ z + q + G.T @ lam + (E.T @ y if len(e) else 0.0)
-        rpi = G @ z + s - h
-        if max(np.abs(rd).max(), np.abs(rpi).max()) > 1e-5 * scale:
-            status = INFEASIBLE
-
+        zp = np.zeros(n)
+        N = np.eye(n)
+    Hr = N.T @ P @ N
+    Hr = 0.5 * (Hr + Hr.T)
+    gr = N.T @ (P @ zp + q)
+    Gr = G @ N
+    hr = h - G @ zp
+    # rows that do not depend on the free variables are constants: satisfied or infeasible
+    rown = np.abs(Gr).max(axis=1) if Gr.size else np.zeros(0)
+    const = rown < 1e-12
+    if (hr[const] < -1e-9).any():
+        return dict(z=zp, y=None, lam=np.zeros(len(h)), s=hr, status=INFEASIBLE, iters=0, polished=False)
+    keep = ~const
+    w, s, lam_k, status, it = _ipm_ineq(Hr, gr, Gr[keep], hr[keep], tol, max_iter)
     polished = False
-    if status != INFEASIBLE and do_polish:
-        z, y, lam, polished = polish(P, q, E, e, G, h, z, y, lam)
-        if polished:
-            s = h - G @ z
-    return dict(z=z, y=y, lam=lam, s=s, status=status, iters=it, polished=polished)
+    if status != INFEASIBLE and do_polish and keep.any():
+        w, lam_k, polished = _polish_ineq(Hr, gr, Gr[keep], hr[keep], w, lam_k)
+    lam = np.zeros(len(h))
+    lam[keep] = lam_k
+    z = zp + N @ w
+    return dict(z=z, y=None, lam=lam, s=h - G @ z, status=status, iters=it, polished=polished)
