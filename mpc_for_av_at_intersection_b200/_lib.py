@@ -1,0 +1,102 @@
+"""ctypes binding of libmpcb.so (include/mpcb.h).  There is no fallback: if the shared library is
+missing or no CUDA device is usable, the product raises."""
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmpcb.so")
+CSRC = os.path.join(_HERE, "csrc")
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-shared", "-Xcompiler", "-fPIC"]
+
+
+class MpcbError(RuntimeError):
+    pass
+
+
+class mpcb_config(C.Structure):
+    _fields_ = [
+        ("T", C.c_int), ("max_iter", C.c_int),
+        ("w_perp", C.c_double), ("w_para", C.c_double),
+        ("R", C.c_double * 2), ("Rd", C.c_double * 2), ("Q_v_yaw", C.c_double * 2), ("Qf", C.c_double * 4),
+        ("goal_dis", C.c_double), ("stop_speed", C.c_double), ("max_dsteer_deg", C.c_double),
+        ("max_accel", C.c_double), ("max_decel", C.c_double), ("max_steer", C.c_double),
+        ("max_speed", C.c_double), ("min_speed", C.c_double), ("r_end", C.c_double),
+        ("min_ref_speed", C.c_double), ("dt", C.c_double), ("wheelbase", C.c_double),
+        ("ipm_max_iter", C.c_int), ("ipm_tol_mu", C.c_double), ("ipm_tol_p", C.c_double),
+        ("ipm_tol_d", C.c_double),
+    ]
+
+
+EXPORTS = [
+    "mpcb_version", "mpcb_default_config", "mpcb_device_count", "mpcb_create", "mpcb_destroy",
+    "mpcb_last_error", "mpcb_supported_horizons", "mpcb_smooth_yaw", "mpcb_set_courses_host", "mpcb_step",
+    "mpcb_step_host", "mpcb_plant_step", "mpcb_is_goal", "mpcb_launch_count", "mpcb_measure_fp64_peak",
+]
+
+
+def build(verbose=False):
+    """Compile libmpcb.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith(".cu")]
+    deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")] + \
+        [os.path.join(_HERE, "..", "include", "mpcb.h")]
+    if os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
+        return LIB_PATH
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + srcs
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise MpcbError("nvcc failed:\n" + res.stderr[-4000:])
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise MpcbError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, ip, dp = C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double)
+    L.mpcb_version.restype = C.c_int
+    L.mpcb_default_config.argtypes = [C.POINTER(mpcb_config)]
+    L.mpcb_default_config.restype = None
+    L.mpcb_device_count.restype = C.c_int
+    L.mpcb_create.argtypes = [C.POINTER(mpcb_config), C.c_int, C.c_int, C.POINTER(vp)]
+    L.mpcb_create.restype = C.c_int
+    L.mpcb_destroy.argtypes = [vp]
+    L.mpcb_destroy.restype = None
+    L.mpcb_last_error.argtypes = [vp]
+    L.mpcb_last_error.restype = C.c_char_p
+    L.mpcb_supported_horizons.argtypes = [ip, C.c_int]
+    L.mpcb_supported_horizons.restype = C.c_int
+    L.mpcb_smooth_yaw.argtypes = [vp, C.c_int]
+    L.mpcb_smooth_yaw.restype = None
+    L.mpcb_set_courses_host.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int]
+    L.mpcb_set_courses_host.restype = C.c_int
+    L.mpcb_step.argtypes = [vp, C.c_int] + [vp] * 15
+    L.mpcb_step.restype = C.c_int
+    L.mpcb_step_host.argtypes = [vp, C.c_int] + [vp] * 14
+    L.mpcb_step_host.restype = C.c_int
+    L.mpcb_plant_step.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp]
+    L.mpcb_plant_step.restype = C.c_int
+    L.mpcb_is_goal.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp, vp]
+    L.mpcb_is_goal.restype = C.c_int
+    L.mpcb_launch_count.argtypes = [vp]
+    L.mpcb_launch_count.restype = C.c_longlong
+    L.mpcb_measure_fp64_peak.argtypes = [C.c_int, dp]
+    L.mpcb_measure_fp64_peak.restype = C.c_int
+    _lib = L
+    return L
+
+
+def check(rc, handle=None, what=""):
+    if rc != 0:
+        msg = lib().mpcb_last_error(handle)
+        raise MpcbError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")

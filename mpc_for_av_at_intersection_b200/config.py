@@ -1,0 +1,70 @@
+"""MPC configuration: the JSON schema of the reference (main/config/mpc_config.json, 17 keys) and its
+POD mirror for the C ABI (include/mpcb.h: mpcb_config)."""
+import json
+import os
+from dataclasses import dataclass, field
+from typing import List
+
+from . import _lib
+
+_DEFAULT_JSON = os.path.join(os.path.dirname(os.path.abspath(__file__)), "config", "mpc_config.json")
+
+
+@dataclass
+class MpcConfig:
+    NX: int = 4
+    NU: int = 2
+    T: int = 13
+    w_perp: float = 20.0
+    w_para: float = 1.0
+    R: List[float] = field(default_factory=lambda: [0.01, 0.01])
+    Rd: List[float] = field(default_factory=lambda: [0.01, 1.0])
+    Q_v_yaw: List[float] = field(default_factory=lambda: [0.0, 0.5])
+    Qf: List[float] = field(default_factory=lambda: [1.0, 1.0, 0.0, 0.5])     # as in the file: unscaled
+    GOAL_DIS: float = 1.5
+    STOP_SPEED: float = 0.1389
+    MAX_TIME: float = 13.0        # unused by the reference too
+    MAX_ITER: int = 1
+    DU_TH: float = 0.1            # unused by the reference too (early exit is commented out, mpc.py:231-237)
+    MAX_DSTEER: float = 30.0      # deg/s as in the file
+    MAX_ACCEL: float = 2.0
+    MAX_DECEL: float = -10.0
+    # not in the JSON: arguments of MPC.__init__ / car dimensions, and solver controls
+    dt: float = 0.2
+    wheelbase: float = 2.86
+    ipm_max_iter: int = 40
+    ipm_tol_mu: float = 1e-12
+    ipm_tol_p: float = 1e-10
+    ipm_tol_d: float = 1e-9
+
+    @staticmethod
+    def from_json(path=None, **overrides):
+        with open(path or _DEFAULT_JSON, "r") as f:
+            d = json.load(f)
+        return MpcConfig.from_dict({**d, **overrides})
+
+    @staticmethod
+    def from_dict(d):
+        known = set(MpcConfig.__dataclass_fields__)
+        unknown = set(d) - known
+        if unknown:
+            raise KeyError(f"unknown mpc_config keys: {sorted(unknown)}")
+        return MpcConfig(**d)
+
+    def to_c(self):
+        c = _lib.mpcb_config()
+        _lib.lib().mpcb_default_config(c)
+        if self.NX != 4 or self.NU != 2:
+            raise ValueError("only NX=4, NU=2 (main/lib/mpc.py) is supported")
+        c.T, c.max_iter = int(self.T), int(self.MAX_ITER)
+        c.w_perp, c.w_para = float(self.w_perp), float(self.w_para)
+        for i in range(2):
+            c.R[i], c.Rd[i], c.Q_v_yaw[i] = float(self.R[i]), float(self.Rd[i]), float(self.Q_v_yaw[i])
+        for i in range(4):
+            c.Qf[i] = float(self.Qf[i])
+        c.goal_dis, c.stop_speed = float(self.GOAL_DIS), float(self.STOP_SPEED)
+        c.max_dsteer_deg, c.max_accel, c.max_decel = float(self.MAX_DSTEER), float(self.MAX_ACCEL), float(self.MAX_DECEL)
+        c.dt, c.wheelbase = float(self.dt), float(self.wheelbase)
+        c.ipm_max_iter = int(self.ipm_max_iter)
+        c.ipm_tol_mu, c.ipm_tol_p, c.ipm_tol_d = float(self.ipm_tol_mu), float(self.ipm_tol_p), float(self.ipm_tol_d)
+        return c

@@ -1,0 +1,87 @@
+// mpcb_common.cuh -- parameter block and warp-level helpers shared by the sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define MPCB_FULL 0xffffffffu
+
+// Everything a step kernel needs, passed by value (lives in the constant bank of the launch).
+struct StepParams {
+    int B, R, ncmax;
+    const double* courses;   // [R][3][ncmax]  x | y | yaw(smoothed)
+    const double* dl;        // [R]
+    const double* state;     // [B,4] x y yaw v
+    const int* route;        // [B]
+    const int* ncourse;      // [B]
+    const double* L;         // [B] or nullptr
+    int* target_ind;         // [B] io
+    int* warm;               // [B] io
+    double* oa;              // [B,T] io
+    double* od;              // [B,T] io
+    double* traj;            // [B,4,T+1] out (may be null)
+    double* xref;            // [B,4,T+1] out (may be null)
+    double* di_ai;           // [B,2] io
+    double* xdev;            // [B] out (may be null)
+    int* status;             // [B] out
+    int* iters;              // [B] out (may be null)
+    // config (main/config/mpc_config.json after main/lib/mpc.py:17-36)
+    double w_perp, w_para, R0, R1, Rd0, Rd1, Qv, Qyaw, Qf0, Qf1, Qf2, Qf3;   // Qf* already scaled by T
+    double dsteer_dt;        // MAX_DSTEER[rad/s] * dt
+    double max_accel, max_decel, max_steer, max_speed, min_speed, r_end, min_ref_speed, dt, wheelbase;
+    int max_iter, ipm_max_iter;
+    double tol_mu, tol_p, tol_d;
+};
+
+namespace mpcb {
+
+__device__ __forceinline__ double shfl(double v, int src) { return __shfl_sync(MPCB_FULL, v, src); }
+__device__ __forceinline__ double shfl_up1(double v, int lane) {
+    double n = __shfl_up_sync(MPCB_FULL, v, 1);
+    return lane >= 1 ? n : 0.0;
+}
+__device__ __forceinline__ double shfl_dn1(double v, int lane) {
+    double n = __shfl_down_sync(MPCB_FULL, v, 1);
+    return lane < 31 ? n : 0.0;
+}
+// inclusive prefix sum over lanes 0..lane
+__device__ __forceinline__ double scan_up(double v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        double n = __shfl_up_sync(MPCB_FULL, v, d);
+        if (lane >= d) v += n;
+    }
+    return v;
+}
+// inclusive suffix sum over lanes lane..31
+__device__ __forceinline__ double scan_dn(double v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        double n = __shfl_down_sync(MPCB_FULL, v, d);
+        if (lane + d < 32) v += n;
+    }
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(MPCB_FULL, v, d);
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) v = fmax(v, __shfl_xor_sync(MPCB_FULL, v, d));
+    return v;
+}
+// reciprocal: hardware seed (about 20 bits) + two Newton steps; operands here are pivots and
+// slacks, far from the subnormal range, so the flush-to-zero seed is safe.
+__device__ __forceinline__ double rcp(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    return r;
+}
+__device__ __forceinline__ double clampd(double v, double lo, double hi) { return fmax(fmin(v, hi), lo); }
+
+}  // namespace mpcb

@@ -1,0 +1,575 @@
+// mpcb_step.cuh -- the fused MPC step: one warp per problem, lane t <-> horizon stage t.
+//
+// Replaces, per problem, main/lib/mpc.py:211-239 (_iterative_linear_mpc_control):
+//   A2  reference lookup      main/lib/mpc.py:86-109, main/lib/trajectories.py:100-126
+//   A3  bicycle rollout       main/lib/mpc.py:112-126, main/lib/simulation.py:35-47, main/bicycle/main.py:28-41
+//   A4  linearisation         main/lib/mpc.py:58-79 (steer operating point 0)
+//   A5  cost assembly         main/lib/mpc.py:151-184, condensed onto the inputs
+//   A6  constraints + solve   main/lib/mpc.py:184-208; Mehrotra interior point, LDL' of H + G'WG
+//   A7  bookkeeping           main/lib/mpc.py:289-299
+//
+// Math (derived and checked in oracle/condensed_model.py): inputs u = [a_0..a_{T-1} | d_0..d_{T-1}].
+//   v_t   = v_0 + dt * sum_{k<t} a_k                 phi_t = phi_0 + sum_{k<t} b_k d_k,  b_k = dt*vbar_k/L
+//   x_t+1 = x_t + c_t v_t - p_t (phi_t - phibar_t)   c = dt cos(phibar), p = dt vbar sin(phibar)
+//   y_t+1 = y_t + s_t v_t + q_t (phi_t - phibar_t)   s = dt sin(phibar), q = dt vbar cos(phibar)
+// so d pos_t/d a_k = dt (Z_t - Z_{k+1}), d pos_t/d d_k = b_k (W_t - W_{k+1}) with Z, W prefix sums of
+// (c,s) and (-p,q); every Hessian entry is a combination of SUFFIX sums of moments of the 2x2 stage
+// weights evaluated at max(i,j)+1, and the gradient is one forward + one adjoint scan.  The 8T-2
+// inequality rows (accel box, steer box, steer rate, speed bounds as prefix sums) are never stored.
+//
+// Matrix layout: M = [[A, B'], [B, C]] (A = accel block, C = steer block, B = d/a cross block).
+// Lane i keeps row i of A, B and C in registers (3T doubles).  Right-looking LDL': at step k every
+// lane publishes its (unscaled) column-k entry to shared memory, which is at the same time the
+// broadcast buffer of the rank-1 update and the column-major factor used by the triangular solves.
+#pragma once
+#include "mpcb_common.cuh"
+
+#define MPCB_ST_OPTIMAL 0
+#define MPCB_ST_INACCURATE 1
+#define MPCB_ST_FAILED 2
+#define MPCB_ST_NEAREST 3
+
+namespace mpcb {
+
+template <int T>
+struct WarpSmem {
+    static constexpr int N = 2 * T;
+    static constexpr int LS = 2 * T + 1;      // odd column stride: conflict-free row reads in the back solve
+    double H[3 * T][T];                        // [slot][lane]: A row | B row | C row of the cost Hessian
+    double Lc[N][LS];                          // Lc[k][i] = unscaled column k of the factor (rows i >= k)
+    double inv[N];                             // 1 / d_k
+    double z[N];                               // broadcast slot of the fused forward solve
+    double bc[8][T + 1];                       // per-stage broadcast tables used while assembling H
+};
+
+// top-3 insertion keeping (d, idx) ascending; ties keep the earlier (lower) index first
+__device__ __forceinline__ void top3_insert(double d, int i, double (&bd)[3], int (&bi)[3]) {
+    if (d < bd[2]) {
+        if (d < bd[1]) {
+            bd[2] = bd[1]; bi[2] = bi[1];
+            if (d < bd[0]) { bd[1] = bd[0]; bi[1] = bi[0]; bd[0] = d; bi[0] = i; }
+            else { bd[1] = d; bi[1] = i; }
+        } else { bd[2] = d; bi[2] = i; }
+    }
+}
+
+// main/lib/trajectories.py:100-126, forward=True.  Returns the new index or -1 ("something wrong").
+// Squared distances, no FMA contraction, so that the ordering is the reference's.
+__device__ __forceinline__ int nearest_index_in_direction(const double* __restrict__ cx,
+                                                          const double* __restrict__ cy, int start, int nc,
+                                                          double x, double y, int lane) {
+    const int n = nc - start;
+    if (n <= 1) return start;
+    if (n == 2) return start + 1;
+    double bd[3] = {1e300, 1e300, 1e300};
+    int bi[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
+    for (int j = start + lane; j < nc; j += 32) {
+        const double dx = __dsub_rn(cx[j], x), dy = __dsub_rn(cy[j], y);
+        const double d = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+        top3_insert(d, j, bd, bi);
+    }
+    int ind[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        // warp arg-min on (distance, index)
+        double d = bd[0];
+        int i = bi[0];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            const double d2 = __shfl_xor_sync(MPCB_FULL, d, o);
+            const int i2 = __shfl_xor_sync(MPCB_FULL, i, o);
+            if (d2 < d || (d2 == d && i2 < i)) { d = d2; i = i2; }
+        }
+        ind[r] = i;
+        if (bi[0] == i) {   // this lane held the winner: pop it
+            bd[0] = bd[1]; bi[0] = bi[1];
+            bd[1] = bd[2]; bi[1] = bi[2];
+            bd[2] = 1e300; bi[2] = 0x7fffffff;
+        }
+    }
+    if (abs(ind[1] - ind[2]) == 2) return ind[0];
+    if (abs(ind[0] - ind[1]) == 1) return max(ind[0], ind[1]);
+    return -1;
+}
+
+}  // namespace mpcb
+
+namespace mpcb {
+
+// ---- structured constraint operator ------------------------------------------------------------
+// slots per stage t: 0: a<=amax  1: -a<=-amin  2: d<=smax  3: -d<=smax
+//                    4: d[t+1]-d[t]<=r  5: -(d[t+1]-d[t])<=r  (t<=T-2)   6: v[t+1]<=vmax  7: -v[t+1]<=-vmin
+// main/lib/mpc.py:184,187-191; the v[0] rows are constants (x[:,0]==x0) and are checked separately.
+template <int T>
+__device__ __forceinline__ void G_apply(double a, double d, double dt, int lane, double (&g)[8]) {
+    const double dn = shfl_dn1(d, lane);
+    const double dd = (lane < T - 1) ? dn - d : 0.0;
+    const double cs = dt * scan_up(a, lane);
+    g[0] = a; g[1] = -a; g[2] = d; g[3] = -d; g[4] = dd; g[5] = -dd; g[6] = cs; g[7] = -cs;
+}
+template <int T>
+__device__ __forceinline__ void GT_apply(const double (&y)[8], double dt, int lane, double& ga, double& gd) {
+    ga = y[0] - y[1] + dt * scan_dn(y[6] - y[7], lane);
+    const double r = y[4] - y[5];
+    gd = y[2] - y[3] - r + shfl_up1(r, lane);
+}
+
+template <int T, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParams p) {
+    static_assert(T >= 3 && T <= 31, "one warp per problem needs T+1 <= 32");
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int b = blockIdx.x * WARPS + wid;
+    if (b >= p.B) return;
+    WarpSmem<T>& sm = reinterpret_cast<WarpSmem<T>*>(smem_raw)[wid];
+    const bool act = lane < T;
+    const double dt = p.dt;
+
+    // ---- problem inputs ------------------------------------------------------------------------
+    const double x0 = p.state[4 * b + 0], y0 = p.state[4 * b + 1], yaw0 = p.state[4 * b + 2], v0 = p.state[4 * b + 3];
+    const int route = p.route[b];
+    const int nc = p.ncourse[b];
+    const double L = p.L ? p.L[b] : p.wheelbase;
+    const double dl = p.dl[route];
+    const double* __restrict__ cx = p.courses + (size_t)route * 3 * p.ncmax;
+    const double* __restrict__ cy = cx + p.ncmax;
+    const double* __restrict__ cyaw = cy + p.ncmax;
+    int tind = p.target_ind[b];
+    const int warm = p.warm[b];
+    double oa = (warm && act) ? p.oa[(size_t)b * T + lane] : 0.0;     // mpc.py:222-224
+    double od = (warm && act) ? p.od[(size_t)b * T + lane] : 0.0;
+
+    int status = MPCB_ST_OPTIMAL, iters = 0;
+    bool solved = false, have_ov = false;
+    double sx = 0.0, sy = 0.0, sv = 0.0, sph = 0.0;    // solution states at index lane (0..T)
+    double xr_x = 0.0, xr_y = 0.0, xr_yaw = 0.0;       // xref at state index lane (0..T)
+
+    for (int pass = 0; pass < p.max_iter; ++pass) {
+        // ---- A2: reference lookup -----------------------------------------------------------------
+        const int ni = nearest_index_in_direction(cx, cy, tind, nc, x0, y0, lane);
+        if (ni < 0) { status = MPCB_ST_NEAREST; break; }
+        tind = ni;
+        double trav = 0.0;
+        if (!have_ov) {
+            const double pstep = __dmul_rn(fabs(fmax(v0, p.min_ref_speed)), dt);    // |ov| * dt, mpc.py:96-98
+            double acc = 0.0;
+#pragma unroll
+            for (int i = 0; i <= T; ++i) {
+                acc = (i == 0) ? pstep : __dadd_rn(acc, pstep);                     // np.cumsum is sequential
+                if (i == lane) trav = acc;
+            }
+        } else {
+            const double term = __dmul_rn(fabs(sv), dt);
+            double acc = 0.0;
+#pragma unroll
+            for (int i = 0; i <= T; ++i) {
+                const double ti = shfl(term, i);
+                acc = (i == 0) ? ti : __dadd_rn(acc, ti);
+                if (i == lane) trav = acc;
+            }
+        }
+        int idx = (int)rint(__ddiv_rn(trav, dl)) + tind;    // np.rint: half to even
+        idx = min(idx, nc - 1);
+        if (lane > T) idx = nc - 1;
+        idx = max(idx, 0);
+        xr_x = cx[idx]; xr_y = cy[idx]; xr_yaw = cyaw[idx];
+        const bool reach = (idx == nc - 1);
+
+        // ---- A3: rollout of the previous (unshifted) solution: operating point (vbar, phibar) -------
+        const double dcl = clampd(od, -p.max_steer, p.max_steer);
+        const double tnd = act ? tan(dcl) : 0.0;
+        double vb = v0, vcur = v0;
+#pragma unroll
+        for (int t = 0; t < T - 1; ++t) {
+            const double at = shfl(oa, t);
+            vcur = clampd(__dadd_rn(vcur, __dmul_rn(at, dt)), p.min_speed, p.max_speed);
+            if (lane == t + 1) vb = vcur;
+        }
+        const double yterm = __dmul_rn(__dmul_rn(__ddiv_rn(vb, L), tnd), dt);
+        double pb = yaw0, pcur = yaw0;
+#pragma unroll
+        for (int t = 0; t < T - 1; ++t) {
+            pcur = __dadd_rn(pcur, shfl(yterm, t));
+            if (lane == t + 1) pb = pcur;
+        }
+
+        // ---- A4: linearisation coefficients of stage `lane` -----------------------------------------
+        double sn, cs;
+        sincos(pb, &sn, &cs);
+        const double dtv = dt * vb;
+        const double c_ = act ? dt * cs : 0.0, s_ = act ? dt * sn : 0.0;
+        const double pp = act ? dtv * sn : 0.0, qq = act ? dtv * cs : 0.0;
+        const double bb = act ? dtv / L : 0.0;
+        if (!act) pb = 0.0;
+        const double cn = shfl_dn1(c_, lane), snn = shfl_dn1(s_, lane), ppn = shfl_dn1(pp, lane), qqn = shfl_dn1(qq, lane);
+
+        // ---- A5: stage weights for state lane+1, input weights for stage lane -------------------------
+        const double rx = shfl_dn1(xr_x, lane), ry = shfl_dn1(xr_y, lane), rpsi = shfl_dn1(xr_yaw, lane);
+        const bool reach_n = __shfl_down_sync(MPCB_FULL, (int)reach, 1) != 0;
+        double m11 = 0.0, m12 = 0.0, m22 = 0.0, wv = 0.0, wp = 0.0;
+        if (act) {
+            if (!reach_n) {
+                double s1, c1, s2, c2;
+                sincos(rpsi + 0.5 * 3.141592653589793, &s1, &c1);     // mpc.py:160
+                sincos(rpsi, &s2, &c2);                                // mpc.py:164
+                m11 = p.w_perp * (c1 * c1) + p.w_para * (c2 * c2);
+                m12 = p.w_perp * (c1 * s1) + p.w_para * (c2 * s2);
+                m22 = p.w_perp * (s1 * s1) + p.w_para * (s2 * s2);
+                wv = p.Qv; wp = p.Qyaw;
+            } else { m11 = p.Qf0; m22 = p.Qf1; wv = p.Qf2; wp = p.Qf3; }
+        }
+        const double ra_w = act ? (reach ? p.r_end : p.R0) : 0.0;     // mpc.py:177-180
+        const double rd_w = act ? (reach ? p.r_end : p.R1) : 0.0;
+
+        // ---- condensed Hessian from suffix moments ----------------------------------------------------
+        const double Zx = scan_up(c_, lane), Zy = scan_up(s_, lane);
+        const double Wx = scan_up(-pp, lane), Wy = scan_up(qq, lane);
+        {
+            const double MZx = m11 * Zx + m12 * Zy, MZy = m12 * Zx + m22 * Zy;
+            const double MWx = m11 * Wx + m12 * Wy, MWy = m12 * Wx + m22 * Wy;
+            const double S11 = scan_dn(m11, lane), S12 = scan_dn(m12, lane), S22 = scan_dn(m22, lane);
+            const double S1zx = scan_dn(MZx, lane), S1zy = scan_dn(MZy, lane);
+            const double S1wx = scan_dn(MWx, lane), S1wy = scan_dn(MWy, lane);
+            const double S2zz = scan_dn(Zx * MZx + Zy * MZy, lane);
+            const double S2ww = scan_dn(Wx * MWx + Wy * MWy, lane);
+            const double S2wz = scan_dn(Wx * MZx + Wy * MZy, lane);
+            const double Sv = scan_dn(wv, lane), Sp = scan_dn(wp, lane);
+            const double gAx = S11 * Zx + S12 * Zy - S1zx, gAy = S12 * Zx + S22 * Zy - S1zy;
+            const double gCx = S11 * Wx + S12 * Wy - S1wx, gCy = S12 * Wx + S22 * Wy - S1wy;
+            const double hA = S2zz - (Zx * S1zx + Zy * S1zy) + Sv;
+            const double hC = S2ww - (Wx * S1wx + Wy * S1wy) + Sp;
+            const double hB = S2wz - (Wx * S1zx + Wy * S1zy);
+            const double hh = S2wz - (Zx * S1wx + Zy * S1wy);
+            __syncwarp();
+            if (act) {
+                sm.bc[0][lane] = Zx; sm.bc[1][lane] = Zy; sm.bc[2][lane] = Wx; sm.bc[3][lane] = Wy;
+                sm.bc[4][lane] = bb; sm.bc[5][lane] = hh; sm.bc[6][lane] = gAx; sm.bc[7][lane] = gAy;
+            }
+            __syncwarp();
+            const double kA = 2.0 * dt * dt, kB = 2.0 * bb * dt, kC = 2.0 * bb;
+            const int nb = (lane > 0 ? 1 : 0) + (lane < T - 1 ? 1 : 0);
+#pragma unroll
+            for (int j = 0; j < T; ++j) {
+                const double zxj = sm.bc[0][j], zyj = sm.bc[1][j], wxj = sm.bc[2][j], wyj = sm.bc[3][j];
+                double Aij = kA * (hA + zxj * gAx + zyj * gAy);
+                double Cij = kC * sm.bc[4][j] * (hC + wxj * gCx + wyj * gCy);
+                const double Blo = hB + zxj * gCx + zyj * gCy;
+                const double Bup = sm.bc[5][j] + Wx * sm.bc[6][j] + Wy * sm.bc[7][j];
+                const double Bij = kB * ((j <= lane) ? Blo : Bup);
+                if (j == lane) { Aij += 2.0 * ra_w + 2.0 * p.Rd0 * nb; Cij += 2.0 * rd_w + 2.0 * p.Rd1 * nb; }
+                if (j == lane - 1) { Aij -= 2.0 * p.Rd0; Cij -= 2.0 * p.Rd1; }
+                if (act) { sm.H[j][lane] = Aij; sm.H[T + j][lane] = Bij; sm.H[2 * T + j][lane] = Cij; }
+            }
+            __syncwarp();
+        }
+
+        // ---- linear prediction and objective gradient by scans ------------------------------------------
+        // returns the states at index lane+1 (lanes < T); see oracle/condensed_model.py states()/grad()
+        auto predict = [&](double a, double d, double& xs, double& ys, double& vs, double& phs) {
+            const double sa = scan_up(a, lane);
+            const double bd_ = bb * d;
+            const double sp_ = scan_up(bd_, lane);
+            vs = v0 + dt * sa;
+            phs = yaw0 + sp_;
+            const double vt = v0 + dt * (sa - a);
+            const double dph = (yaw0 + (sp_ - bd_)) - pb;
+            xs = x0 + scan_up(c_ * vt - pp * dph, lane);
+            ys = y0 + scan_up(s_ * vt + qq * dph, lane);
+        };
+        auto gradient = [&](double a, double d, double& ga, double& gd) {
+            double xs, ys, vs, phs;
+            predict(a, d, xs, ys, vs, phs);
+            const double ex = xs - rx, ey = ys - ry;
+            const double lx = 2.0 * (m11 * ex + m12 * ey), ly = 2.0 * (m12 * ex + m22 * ey);
+            const double lv = 2.0 * wv * vs, lp = 2.0 * wp * (phs - rpsi);      // xref[2,:] = 0 (mpc.py:102-105)
+            const double px = scan_dn(lx, lane), py = scan_dn(ly, lane);
+            const double pxn = shfl_dn1(px, lane), pyn = shfl_dn1(py, lane);
+            const double pv = scan_dn(lv + cn * pxn + snn * pyn, lane);
+            const double pph = scan_dn(lp - ppn * pxn + qqn * pyn, lane);
+            const double ap = shfl_up1(a, lane), an = shfl_dn1(a, lane);
+            const double dp = shfl_up1(d, lane), dn = shfl_dn1(d, lane);
+            const double fa = (lane > 0 ? a - ap : 0.0) - (lane < T - 1 ? an - a : 0.0);
+            const double fd = (lane > 0 ? d - dp : 0.0) - (lane < T - 1 ? dn - d : 0.0);
+            ga = act ? dt * pv + 2.0 * ra_w * a + 2.0 * p.Rd0 * fa : 0.0;
+            gd = act ? bb * pph + 2.0 * rd_w * d + 2.0 * p.Rd1 * fd : 0.0;
+        };
+
+        // ---- A6: interior point on  min J(u)  s.t.  G u <= h ----------------------------------------------
+        double hh8[8];
+        hh8[0] = p.max_accel; hh8[1] = -p.max_decel; hh8[2] = p.max_steer; hh8[3] = p.max_steer;
+        hh8[4] = p.dsteer_dt; hh8[5] = p.dsteer_dt; hh8[6] = p.max_speed - v0; hh8[7] = v0 - p.min_speed;
+        bool mk[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) mk[c] = (c == 4 || c == 5) ? (lane < T - 1) : act;
+        const double m_cnt = 8.0 * T - 2.0;
+        // x[2,0] <= MAX_SPEED and >= MIN_SPEED are constant rows (mpc.py:186-188): infeasible if violated
+        bool feasible0 = (hh8[6] >= -1e-9) && (hh8[7] >= -1e-9);
+
+        double a = oa, d = od;
+        double s[8], lam[8];
+        {
+            double g[8];
+            G_apply<T>(a, d, dt, lane, g);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                s[c] = mk[c] ? fmax(hh8[c] - g[c], 1.0) : 1.0;
+                lam[c] = mk[c] ? 1.0 : 0.0;
+            }
+        }
+        double gscale;
+        {
+            double g0a, g0d;
+            gradient(0.0, 0.0, g0a, g0d);
+            gscale = 1.0 + warp_max(fmax(fabs(g0a), fabs(g0d)));
+        }
+        double res_d = 1e300, res_p = 1e300, mu = 1e300;
+        bool converged = false, broke = false;
+        int it = 0;
+        for (; feasible0; ++it) {
+            double rda, rdd, rp[8];
+            {
+                double ga, gd, gta, gtd, g[8];
+                gradient(a, d, ga, gd);
+                GT_apply<T>(lam, dt, lane, gta, gtd);
+                rda = ga + gta; rdd = gd + gtd;
+                G_apply<T>(a, d, dt, lane, g);
+                double sl = 0.0, rpm = 0.0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    rp[c] = mk[c] ? g[c] + s[c] - hh8[c] : 0.0;
+                    sl += s[c] * lam[c];
+                    rpm = fmax(rpm, fabs(rp[c]));
+                }
+                mu = warp_sum(sl) / m_cnt;
+                res_d = warp_max(fmax(fabs(rda), fabs(rdd)));
+                res_p = warp_max(rpm);
+            }
+            if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) { converged = true; break; }
+            if (it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) break;
+
+            // ---- M = H + G' W G into registers (rows `lane` of A, B, C) ---------------------------------
+            double sinv[8], w[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) { sinv[c] = rcp(s[c]); w[c] = lam[c] * sinv[c]; }
+            double A[T], Bm[T], C[T];
+            {
+                const double wv_suf = dt * dt * scan_dn(w[6] + w[7], lane);   // dt^2 * sum_{t>=lane}
+                const double wr = w[4] + w[5];
+                const double wr_prev = shfl_up1(wr, lane);
+                const double dA = w[0] + w[1], dC = w[2] + w[3] + wr + wr_prev;
+#pragma unroll
+                for (int j = 0; j < T; ++j) {
+                    A[j] = (act ? sm.H[j][lane] : 0.0) + wv_suf + (j == lane ? dA : 0.0);
+                    Bm[j] = act ? sm.H[T + j][lane] : 0.0;
+                    C[j] = (act ? sm.H[2 * T + j][lane] : 0.0) + (j == lane ? dC : 0.0) - (j == lane - 1 ? wr_prev : 0.0);
+                }
+            }
+            // affine right-hand side: -r_d + G'(lam - W r_p)
+            double ra, rdl;
+            {
+                double y[8], ya, yd;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) y[c] = lam[c] - w[c] * rp[c];
+                GT_apply<T>(y, dt, lane, ya, yd);
+                ra = ya - rda; rdl = yd - rdd;
+            }
+            // ---- LDL' factorisation, forward solve fused ---------------------------------------------------
+            bool bad = false;
+#pragma unroll
+            for (int k = 0; k < T; ++k) {
+                if (act && lane >= k) sm.Lc[k][lane] = A[k];
+                if (act) sm.Lc[k][T + lane] = Bm[k];
+                if (lane == k) {
+                    bad = bad || !(A[k] > 0.0);
+                    sm.inv[k] = rcp(A[k]);
+                    sm.z[k] = ra;
+                }
+                __syncwarp();
+                const double iv = sm.inv[k];
+                const double zk = sm.z[k] * iv;
+                const double la = A[k] * iv, lb = Bm[k] * iv;
+                if (lane > k) ra -= A[k] * zk;
+                rdl -= Bm[k] * zk;
+#pragma unroll
+                for (int j = k + 1; j < T; ++j) {
+                    const double cj = sm.Lc[k][j];
+                    A[j] -= la * cj;
+                    Bm[j] -= lb * cj;
+                }
+#pragma unroll
+                for (int j = 0; j < T; ++j) C[j] -= lb * sm.Lc[k][T + j];
+            }
+#pragma unroll
+            for (int k = 0; k < T; ++k) {
+                if (act && lane >= k) sm.Lc[T + k][T + lane] = C[k];
+                if (lane == k) {
+                    bad = bad || !(C[k] > 0.0);
+                    sm.inv[T + k] = rcp(C[k]);
+                    sm.z[T + k] = rdl;
+                }
+                __syncwarp();
+                const double iv = sm.inv[T + k];
+                const double zk = sm.z[T + k] * iv;
+                const double lc = C[k] * iv;
+                if (lane > k) rdl -= C[k] * zk;
+#pragma unroll
+                for (int j = k + 1; j < T; ++j) C[j] -= lc * sm.Lc[T + k][T + j];
+            }
+            if (__any_sync(MPCB_FULL, bad)) { broke = true; break; }
+            const double inva = act ? sm.inv[lane] : 0.0, invd = act ? sm.inv[T + lane] : 0.0;
+
+            // back substitution  L' x = D^-1 z  (column-major factor, AXPY form)
+            auto back_solve = [&](double za, double zd, double& xa, double& xd) {
+                const double wa = za * inva, wd = zd * invd;
+                double accA = 0.0, accD = 0.0;
+                xa = 0.0; xd = 0.0;
+#pragma unroll
+                for (int k = T - 1; k >= 0; --k) {
+                    const double xk = shfl(wd - invd * accD, k);
+                    if (lane == k) xd = xk;
+                    if (act) {
+                        if (lane < k) accD += sm.Lc[T + lane][T + k] * xk;
+                        accA += sm.Lc[lane][T + k] * xk;
+                    }
+                }
+#pragma unroll
+                for (int k = T - 1; k >= 0; --k) {
+                    const double xk = shfl(wa - inva * accA, k);
+                    if (lane == k) xa = xk;
+                    if (act && lane < k) accA += sm.Lc[lane][k] * xk;
+                }
+            };
+            auto fwd_solve = [&](double& fa, double& fd) {     // L z = r, factor read from shared memory
+#pragma unroll
+                for (int k = 0; k < T; ++k) {
+                    const double zk = shfl(fa, k) * sm.inv[k];
+                    if (act) {
+                        if (lane > k) fa -= sm.Lc[k][lane] * zk;
+                        fd -= sm.Lc[k][T + lane] * zk;
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < T; ++k) {
+                    const double zk = shfl(fd, k) * sm.inv[T + k];
+                    if (act && lane > k) fd -= sm.Lc[T + k][T + lane] * zk;
+                }
+            };
+
+            // ---- predictor ---------------------------------------------------------------------------------
+            double dsa[8], dla[8];
+            double sigma_mu;
+            {
+                double da, dd, g[8];
+                back_solve(ra, rdl, da, dd);
+                G_apply<T>(da, dd, dt, lane, g);
+                double tmax = 0.0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
+                    dla[c] = mk[c] ? -lam[c] - w[c] * dsa[c] : 0.0;
+                    const double linv = mk[c] ? rcp(lam[c]) : 0.0;
+                    tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
+                }
+                tmax = warp_max(tmax);
+                const double al = 1.0 / fmax(1.0, tmax);
+                double sl = 0.0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) sl += (s[c] + al * dsa[c]) * (lam[c] + al * dla[c]);
+                const double mu_aff = warp_sum(sl) / m_cnt;
+                const double r = mu_aff / mu;
+                sigma_mu = r * r * r * mu;
+            }
+            // ---- corrector ---------------------------------------------------------------------------------
+            {
+                double rc[8], y[8], ya, yd;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    rc[c] = mk[c] ? s[c] * lam[c] + dsa[c] * dla[c] - sigma_mu : 0.0;
+                    y[c] = rc[c] * sinv[c] - w[c] * rp[c];
+                }
+                GT_apply<T>(y, dt, lane, ya, yd);
+                double fa = ya - rda, fd = yd - rdd;
+                fwd_solve(fa, fd);
+                double da, dd, g[8];
+                back_solve(fa, fd, da, dd);
+                G_apply<T>(da, dd, dt, lane, g);
+                double tmax = 0.0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
+                    dla[c] = mk[c] ? -(rc[c] + lam[c] * dsa[c]) * sinv[c] : 0.0;
+                    const double linv = mk[c] ? rcp(lam[c]) : 0.0;
+                    tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
+                }
+                tmax = warp_max(tmax);
+                const double al = (tmax > 0.99) ? 0.99 / tmax : 1.0;
+                a += al * da; d += al * dd;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) { s[c] += al * dsa[c]; lam[c] += al * dla[c]; }
+            }
+        }
+        iters = it;
+        if (converged) status = MPCB_ST_OPTIMAL;
+        else if (feasible0 && res_d < 1e-6 * gscale && res_p < 1e-7 && mu < 1e-7) status = MPCB_ST_INACCURATE;
+        else { status = MPCB_ST_FAILED; solved = false; break; }
+        (void)broke;
+        // solution of this pass: mpc.py:197-202
+        solved = true;
+        oa = a; od = d;
+        {
+            double xs, ys, vs, phs;
+            predict(a, d, xs, ys, vs, phs);
+            // shift so that lane t holds state t; lane 0 holds x0
+            sx = __shfl_up_sync(MPCB_FULL, xs, 1); sy = __shfl_up_sync(MPCB_FULL, ys, 1);
+            sv = __shfl_up_sync(MPCB_FULL, vs, 1); sph = __shfl_up_sync(MPCB_FULL, phs, 1);
+            if (lane == 0) { sx = x0; sy = y0; sv = v0; sph = yaw0; }
+        }
+        have_ov = true;
+    }
+
+    // ---- A7: bookkeeping of MPC.step (main/lib/mpc.py:289-299) -------------------------------------------
+    if (status == MPCB_ST_NEAREST) {          // the reference raises here: nothing of the object changes
+        if (lane == 0) { p.status[b] = status; if (p.iters) p.iters[b] = 0; }
+        return;
+    }
+    const size_t tb = (size_t)b * 4 * (T + 1);
+    if (p.xref && lane <= T) {
+        p.xref[tb + lane] = xr_x;
+        p.xref[tb + (T + 1) + lane] = xr_y;
+        p.xref[tb + 2 * (T + 1) + lane] = 0.0;
+        p.xref[tb + 3 * (T + 1) + lane] = xr_yaw;
+    }
+    const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+    if (solved) {
+        if (act) { p.oa[(size_t)b * T + lane] = oa; p.od[(size_t)b * T + lane] = od; }
+        if (p.traj && lane <= T) {
+            p.traj[tb + lane] = sx;
+            p.traj[tb + (T + 1) + lane] = sy;
+            p.traj[tb + 2 * (T + 1) + lane] = sv;
+            p.traj[tb + 3 * (T + 1) + lane] = sph;
+        }
+    } else if (p.traj && lane <= T) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) p.traj[tb + r * (T + 1) + lane] = qnan;
+    }
+    if (lane == 0) {
+        p.target_ind[b] = tind;
+        p.status[b] = status;
+        if (p.iters) p.iters[b] = iters;
+        p.warm[b] = solved ? 1 : 0;
+        if (solved) { p.di_ai[2 * b] = od; p.di_ai[2 * b + 1] = oa; }
+        else p.di_ai[2 * b + 1] = p.max_decel;                  // mpc.py:296-297, di unchanged
+        if (p.xdev) {
+            // get_current_xref_deviation (mpc.py:301-308): element-wise product, as written there
+            double dev = qnan;
+            if (solved && tind < nc) {
+                const double ang = cyaw[tind] + 3.141592653589793 / 2;
+                const double ex = cos(ang) * (cx[tind] - x0), ey = sin(ang) * (cy[tind] - y0);
+                dev = sqrt(ex * ex + ey * ey);
+            }
+            p.xdev[b] = dev;
+        }
+    }
+}
+
+}  // namespace mpcb
