@@ -131,6 +131,56 @@ int mpcb_plant_step(mpcb_handle* h, int B, double* state_dev, const double* di_a
 int mpcb_is_goal(mpcb_handle* h, int B, const double* state_dev, const double* goal_dev,
                  const int* target_ind_dev, const int* ncourse_dev, int* out_dev, void* stream);
 
+/* ---- resident session -------------------------------------------------------------------------
+ * The reference keeps one `MPC` object per vehicle alive across the closed loop
+ * (main/scenarios/mpc_intersection.py:71,95-159) and mutates it in MPC.step (main/lib/mpc.py:289-292).
+ * A session is the [B,...] device-resident equivalent owned by the handle: per control step only the
+ * vehicle states go in and the applied controls come out; everything else (target_ind, warm start,
+ * ox/oy/ov/oyaw, xref) stays in HBM and is fetched on demand. */
+
+/* fields of the session (mpcb_session_fetch_host / _store_host / _device_ptr) */
+#define MPCB_F_STATE 0    /* double [B,4]      x, y, yaw, v                                  */
+#define MPCB_F_OA 1       /* double [B,T]      mpc.oa                                        */
+#define MPCB_F_OD 2       /* double [B,T]      mpc.odelta                                    */
+#define MPCB_F_TRAJ 3     /* double [B,4,T+1]  mpc.ox, oy, ov, oyaw                          */
+#define MPCB_F_XREF 4     /* double [B,4,T+1]  mpc.xref                                      */
+#define MPCB_F_DI_AI 5    /* double [B,2]      mpc.di, mpc.ai                                */
+#define MPCB_F_XDEV 6     /* double [B]        get_current_xref_deviation()                  */
+#define MPCB_F_TARGET 7   /* int    [B]        mpc.target_ind                                */
+#define MPCB_F_WARM 8     /* int    [B]        mpc.oa is not None                            */
+#define MPCB_F_STATUS 9   /* int    [B]        MPCB_ST_*                                     */
+#define MPCB_F_ITERS 10   /* int    [B]        interior-point iterations                     */
+#define MPCB_F_DONE 11    /* int    [B]        closed loop: 0 running, 1 is_goal, 2 dead (MPCB_ST_NEAREST) */
+#define MPCB_F_NCOURSE 12 /* int    [B]        len(mpc.cx)                                   */
+#define MPCB_F_ROUTE 13   /* int    [B]                                                      */
+#define MPCB_F_GOAL 14    /* double [B,2]      mpc.goal                                      */
+
+/* replaces: constructing B `MPC` objects (main/lib/mpc.py:243-271): target_ind = 0 (or
+ * target_ind_host), oa = odelta = None, di = ai = 0, goal = end of the full course.
+ * ncourse_host NULL = full course lengths; L_host NULL = cfg.wheelbase.  Synchronous. */
+int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* ncourse_host,
+                       const double* L_host, const int* target_ind_host);
+/* replaces: MPC.set_trajectory_fromarray(full[:cutoff]) (main/lib/mpc.py:275-278) for the batch */
+int mpcb_session_set_ncourse_host(mpcb_handle* h, const int* ncourse_host);
+/* replaces: `di, ai = mpc.step(state)` for the batch with HOST buffers: copies state[B,4] in, runs the
+ * step kernel on the resident session, copies di_ai[B,2] (steer, accel) and status[B] (may be NULL)
+ * out.  Synchronous. */
+int mpcb_session_step_host(mpcb_handle* h, const double* state_host, double* di_ai_host, int* status_host);
+/* same step on the state already resident in MPCB_F_STATE; asynchronous on `stream`, capturable */
+int mpcb_session_step_dev(mpcb_handle* h, void* stream);
+/* replaces: the loop body of main/scenarios/mpc_intersection.py:95-159 without obstacles, nsteps
+ * times: is_goal -> break (done=1) | mpc.step | simulation.step, one kernel launch per control step.
+ * history_dev NULL or double [nsteps,B,8] (x, y, yaw, v after the plant step, delta, a,
+ * xref_deviation, status) -- the columns of lib/simulation.py History; rows of finished problems are
+ * left untouched.  flags: MPCB_CL_NO_GOAL_TEST keeps every problem solving on every step (throughput
+ * measurement: no work is skipped).  Asynchronous on `stream`, capturable. */
+#define MPCB_CL_NO_GOAL_TEST 1
+int mpcb_session_closed_loop_dev(mpcb_handle* h, int nsteps, double* history_dev, int flags, void* stream);
+void* mpcb_session_device_ptr(mpcb_handle* h, int what);
+long long mpcb_session_field_bytes(const mpcb_handle* h, int what);
+int mpcb_session_fetch_host(mpcb_handle* h, int what, void* dst, long long bytes);
+int mpcb_session_store_host(mpcb_handle* h, int what, const void* src, long long bytes);
+
 /* kernels launched by this handle so far (bench.py's gpu_launches) */
 long long mpcb_launch_count(const mpcb_handle* h);
 

@@ -33,7 +33,13 @@ EXPORTS = [
     "mpcb_version", "mpcb_default_config", "mpcb_device_count", "mpcb_create", "mpcb_destroy",
     "mpcb_last_error", "mpcb_supported_horizons", "mpcb_smooth_yaw", "mpcb_set_courses_host", "mpcb_step",
     "mpcb_step_host", "mpcb_plant_step", "mpcb_is_goal", "mpcb_launch_count", "mpcb_measure_fp64_peak",
+    "mpcb_session_begin", "mpcb_session_set_ncourse_host", "mpcb_session_step_host", "mpcb_session_step_dev",
+    "mpcb_session_closed_loop_dev", "mpcb_session_device_ptr", "mpcb_session_field_bytes",
+    "mpcb_session_fetch_host", "mpcb_session_store_host",
 ]
+
+F_STATE, F_OA, F_OD, F_TRAJ, F_XREF, F_DI_AI, F_XDEV, F_TARGET, F_WARM, F_STATUS, F_ITERS, F_DONE, F_NCOURSE, \
+    F_ROUTE, F_GOAL = range(15)
 
 
 def build(verbose=False):
@@ -88,6 +94,24 @@ def lib():
     L.mpcb_plant_step.restype = C.c_int
     L.mpcb_is_goal.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp, vp]
     L.mpcb_is_goal.restype = C.c_int
+    L.mpcb_session_begin.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+    L.mpcb_session_begin.restype = C.c_int
+    L.mpcb_session_set_ncourse_host.argtypes = [vp, vp]
+    L.mpcb_session_set_ncourse_host.restype = C.c_int
+    L.mpcb_session_step_host.argtypes = [vp, vp, vp, vp]
+    L.mpcb_session_step_host.restype = C.c_int
+    L.mpcb_session_step_dev.argtypes = [vp, vp]
+    L.mpcb_session_step_dev.restype = C.c_int
+    L.mpcb_session_closed_loop_dev.argtypes = [vp, C.c_int, vp, C.c_int, vp]
+    L.mpcb_session_closed_loop_dev.restype = C.c_int
+    L.mpcb_session_device_ptr.argtypes = [vp, C.c_int]
+    L.mpcb_session_device_ptr.restype = vp
+    L.mpcb_session_field_bytes.argtypes = [vp, C.c_int]
+    L.mpcb_session_field_bytes.restype = C.c_longlong
+    L.mpcb_session_fetch_host.argtypes = [vp, C.c_int, vp, C.c_longlong]
+    L.mpcb_session_fetch_host.restype = C.c_int
+    L.mpcb_session_store_host.argtypes = [vp, C.c_int, vp, C.c_longlong]
+    L.mpcb_session_store_host.restype = C.c_int
     L.mpcb_launch_count.argtypes = [vp]
     L.mpcb_launch_count.restype = C.c_longlong
     L.mpcb_measure_fp64_peak.argtypes = [C.c_int, dp]

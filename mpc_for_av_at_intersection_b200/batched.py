@@ -10,35 +10,13 @@ import torch
 
 from . import _lib
 from .config import MpcConfig
+from .courses import CourseSet  # noqa: F401
 
 ST_OPTIMAL, ST_INACCURATE, ST_FAILED, ST_NEAREST = 0, 1, 2, 3
 
 
 def _ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None else None
-
-
-class CourseSet:
-    """Routes shared by the batch: [R,3,ncmax] (x | y | smoothed yaw), lengths and tick dl."""
-
-    def __init__(self, courses: Sequence[np.ndarray], dl: Optional[Sequence[float]] = None, smooth=True):
-        self.R = len(courses)
-        self.length = np.array([len(c) for c in courses], dtype=np.int32)
-        self.ncmax = int(self.length.max())
-        self.packed = np.zeros((self.R, 3, self.ncmax), dtype=np.float64)
-        lib = _lib.lib()
-        for r, c in enumerate(courses):
-            c = np.ascontiguousarray(np.asarray(c, dtype=np.float64)[:, :3])
-            yaw = np.ascontiguousarray(c[:, 2])
-            if smooth:       # MPC.__init__ smooths cyaw once (main/lib/mpc.py:257)
-                lib.mpcb_smooth_yaw(yaw.ctypes.data_as(C.c_void_p), len(yaw))
-            n = len(c)
-            self.packed[r, 0, :n], self.packed[r, 1, :n], self.packed[r, 2, :n] = c[:, 0], c[:, 1], yaw
-            self.packed[r, :, n:] = self.packed[r, :, n - 1:n]
-        if dl is None:   # dl = |p0 - p1| as main/scenarios/mpc_intersection.py:69
-            dl = [float(np.linalg.norm(np.asarray(c)[0, :2] - np.asarray(c)[1, :2])) for c in courses]
-        self.dl = np.asarray(dl, dtype=np.float64)
-        self.goal = np.array([[self.packed[r, 0, n - 1], self.packed[r, 1, n - 1]] for r, n in enumerate(self.length)])
 
 
 class BatchedMPC:

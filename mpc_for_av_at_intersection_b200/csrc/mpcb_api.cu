@@ -34,6 +34,21 @@ struct mpcb_handle {
     HostStage stage;
     cudaStream_t own_stream = nullptr;
     int smem_optin = 0;
+    int* len_dev = nullptr;
+    std::vector<int> len_host;
+    std::vector<double> goal_host;   // [R,2] last point of each full course (mpc.py:263)
+    // resident session: the [B,...] mirror of the reference's MPC object state lives on the device
+    struct Session {
+        int B = 0;
+        char* slab = nullptr;
+        char* pin = nullptr;        // pinned: state in | di_ai out | status out
+        double *state = nullptr, *L = nullptr, *oa = nullptr, *od = nullptr, *traj = nullptr, *xref = nullptr,
+               *di_ai = nullptr, *xdev = nullptr, *goal = nullptr;
+        int *route = nullptr, *ncourse = nullptr, *target = nullptr, *warm = nullptr, *status = nullptr,
+            *iters = nullptr, *done = nullptr;
+        bool hasL = false;
+        size_t pin_state = 0, pin_diai = 0, pin_status = 0, pin_total = 0;
+    } ses;
 };
 
 #define CUDA_TRY(h, expr)                                                                      \
@@ -132,6 +147,7 @@ StepParams make_params(const mpcb_handle* h) {
     p.max_speed = c.max_speed; p.min_speed = c.min_speed; p.r_end = c.r_end; p.min_ref_speed = c.min_ref_speed;
     p.dt = c.dt; p.wheelbase = c.wheelbase; p.max_iter = c.max_iter; p.ipm_max_iter = c.ipm_max_iter;
     p.tol_mu = c.ipm_tol_mu; p.tol_p = c.ipm_tol_p; p.tol_d = c.ipm_tol_d;
+    p.goal_dis = c.goal_dis; p.stop_speed = c.stop_speed;
     return p;
 }
 
@@ -195,6 +211,9 @@ void mpcb_destroy(mpcb_handle* h) {
     cudaSetDevice(h->device);
     if (h->courses_dev) cudaFree(h->courses_dev);
     if (h->dl_dev) cudaFree(h->dl_dev);
+    if (h->len_dev) cudaFree(h->len_dev);
+    if (h->ses.slab) cudaFree(h->ses.slab);
+    if (h->ses.pin) cudaFreeHost(h->ses.pin);
     if (h->stage.pinned) cudaFreeHost(h->stage.pinned);
     if (h->stage.dev) cudaFree(h->stage.dev);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -212,16 +231,27 @@ void mpcb_smooth_yaw(double* yaw, int n) {
 
 int mpcb_set_courses_host(mpcb_handle* h, const double* courses_host, const int* len_host, const double* dl_host,
                           int R, int ncmax) {
-    if (!h || !courses_host || !dl_host || R <= 0 || ncmax <= 0) { if (h) h->err = "mpcb_set_courses_host: bad arguments"; return MPCB_EINVAL; }
-    (void)len_host;
+    if (!h || !courses_host || !len_host || !dl_host || R <= 0 || ncmax <= 0) { if (h) h->err = "mpcb_set_courses_host: bad arguments"; return MPCB_EINVAL; }
+    for (int r = 0; r < R; ++r)
+        if (len_host[r] < 1 || len_host[r] > ncmax) { h->err = "mpcb_set_courses_host: course length out of range"; return MPCB_EINVAL; }
     CUDA_TRY(h, cudaSetDevice(h->device));
     if (h->courses_dev) { cudaFree(h->courses_dev); h->courses_dev = nullptr; }
     if (h->dl_dev) { cudaFree(h->dl_dev); h->dl_dev = nullptr; }
+    if (h->len_dev) { cudaFree(h->len_dev); h->len_dev = nullptr; }
     const size_t bytes = (size_t)R * 3 * ncmax * sizeof(double);
     CUDA_TRY(h, cudaMalloc(&h->courses_dev, bytes));
     CUDA_TRY(h, cudaMalloc(&h->dl_dev, R * sizeof(double)));
     CUDA_TRY(h, cudaMemcpy(h->courses_dev, courses_host, bytes, cudaMemcpyHostToDevice));
     CUDA_TRY(h, cudaMemcpy(h->dl_dev, dl_host, R * sizeof(double), cudaMemcpyHostToDevice));
+    CUDA_TRY(h, cudaMalloc(&h->len_dev, R * sizeof(int)));
+    CUDA_TRY(h, cudaMemcpy(h->len_dev, len_host, R * sizeof(int), cudaMemcpyHostToDevice));
+    h->len_host.assign(len_host, len_host + R);
+    h->goal_host.resize(2 * (size_t)R);
+    for (int r = 0; r < R; ++r) {
+        const double* c = courses_host + (size_t)r * 3 * ncmax;
+        h->goal_host[2 * r] = c[len_host[r] - 1];
+        h->goal_host[2 * r + 1] = c[ncmax + len_host[r] - 1];
+    }
     h->R = R; h->ncmax = ncmax;
     return MPCB_OK;
 }
@@ -341,6 +371,195 @@ int mpcb_step_host(mpcb_handle* h, int B, const double* state, const int* route,
     if (iters) memcpy(iters, hp + lm.iters, sizeof(int) * B);
     return MPCB_OK;
 }
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// resident session: the batch's MPC object state stays on the device between steps
+// ---------------------------------------------------------------------------------------------------
+namespace {
+
+int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
+    switch (h->cfg.T) {
+        case 10: return launch_step<10, 4>(h, p, st);
+        case 13: return launch_step<13, 4>(h, p, st);
+        case 20: return launch_step<20, 4>(h, p, st);
+        default: h->err = "mpcb: unsupported horizon"; return MPCB_EINVAL;
+    }
+}
+
+int session_alloc(mpcb_handle* h) {
+    auto& s = h->ses;
+    if (s.slab) return MPCB_OK;
+    const size_t B = (size_t)h->max_batch, T = (size_t)h->cfg.T;
+    size_t o = 0;
+    auto put = [&](size_t bytes) { size_t at = o; o = align256(o + bytes); return at; };
+    const size_t o_state = put(8 * 4 * B), o_L = put(8 * B), o_oa = put(8 * T * B), o_od = put(8 * T * B),
+                 o_traj = put(8 * 4 * (T + 1) * B), o_xref = put(8 * 4 * (T + 1) * B), o_diai = put(8 * 2 * B),
+                 o_xdev = put(8 * B), o_goal = put(8 * 2 * B), o_route = put(4 * B), o_nc = put(4 * B),
+                 o_tgt = put(4 * B), o_warm = put(4 * B), o_status = put(4 * B), o_iters = put(4 * B),
+                 o_done = put(4 * B);
+    CUDA_TRY(h, cudaMalloc(&s.slab, o));
+    CUDA_TRY(h, cudaMemset(s.slab, 0, o));
+    char* d = s.slab;
+    s.state = (double*)(d + o_state); s.L = (double*)(d + o_L); s.oa = (double*)(d + o_oa); s.od = (double*)(d + o_od);
+    s.traj = (double*)(d + o_traj); s.xref = (double*)(d + o_xref); s.di_ai = (double*)(d + o_diai);
+    s.xdev = (double*)(d + o_xdev); s.goal = (double*)(d + o_goal); s.route = (int*)(d + o_route);
+    s.ncourse = (int*)(d + o_nc); s.target = (int*)(d + o_tgt); s.warm = (int*)(d + o_warm);
+    s.status = (int*)(d + o_status); s.iters = (int*)(d + o_iters); s.done = (int*)(d + o_done);
+    o = 0;
+    s.pin_state = put(8 * 4 * B); s.pin_diai = put(8 * 2 * B); s.pin_status = put(4 * B);
+    s.pin_total = o;
+    CUDA_TRY(h, cudaMallocHost(&s.pin, s.pin_total));
+    return MPCB_OK;
+}
+
+StepParams session_params(mpcb_handle* h) {
+    auto& s = h->ses;
+    StepParams p = make_params(h);
+    p.B = s.B; p.state = s.state; p.route = s.route; p.ncourse = s.ncourse; p.L = s.hasL ? s.L : nullptr;
+    p.target_ind = s.target; p.warm = s.warm; p.oa = s.oa; p.od = s.od; p.traj = s.traj; p.xref = s.xref;
+    p.di_ai = s.di_ai; p.xdev = s.xdev; p.status = s.status; p.iters = s.iters;
+    return p;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* ncourse_host, const double* L_host,
+                       const int* target_ind_host) {
+    if (!h || B <= 0 || B > h->max_batch || !route_host) { if (h) h->err = "mpcb_session_begin: bad arguments"; return MPCB_EINVAL; }
+    if (!h->courses_dev) { h->err = "mpcb_session_begin: no courses set"; return MPCB_EINVAL; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    int rc = session_alloc(h);
+    if (rc != MPCB_OK) return rc;
+    auto& s = h->ses;
+    std::vector<int> nc(B);
+    std::vector<double> goal(2 * (size_t)B);
+    for (int b = 0; b < B; ++b) {
+        const int r = route_host[b];
+        if (r < 0 || r >= h->R) { h->err = "mpcb_session_begin: route id out of range"; return MPCB_EINVAL; }
+        nc[b] = ncourse_host ? ncourse_host[b] : h->len_host[r];
+        if (nc[b] < 1 || nc[b] > h->len_host[r]) { h->err = "mpcb_session_begin: ncourse out of range"; return MPCB_EINVAL; }
+        goal[2 * b] = h->goal_host[2 * r]; goal[2 * b + 1] = h->goal_host[2 * r + 1];
+    }
+    s.B = B; s.hasL = L_host != nullptr;
+    cudaStream_t st = h->own_stream;
+    CUDA_TRY(h, cudaMemcpyAsync(s.route, route_host, 4 * (size_t)B, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(h, cudaMemcpyAsync(s.ncourse, nc.data(), 4 * (size_t)B, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(h, cudaMemcpyAsync(s.goal, goal.data(), 16 * (size_t)B, cudaMemcpyHostToDevice, st));
+    if (L_host) CUDA_TRY(h, cudaMemcpyAsync(s.L, L_host, 8 * (size_t)B, cudaMemcpyHostToDevice, st));
+    if (target_ind_host) CUDA_TRY(h, cudaMemcpyAsync(s.target, target_ind_host, 4 * (size_t)B, cudaMemcpyHostToDevice, st));
+    else CUDA_TRY(h, cudaMemsetAsync(s.target, 0, 4 * (size_t)B, st));
+    CUDA_TRY(h, cudaMemsetAsync(s.warm, 0, 4 * (size_t)B, st));         // oa = odelta = None (mpc.py:265-266)
+    CUDA_TRY(h, cudaMemsetAsync(s.done, 0, 4 * (size_t)B, st));
+    CUDA_TRY(h, cudaMemsetAsync(s.di_ai, 0, 16 * (size_t)B, st));       // di = ai = 0.0 (mpc.py:270-271)
+    CUDA_TRY(h, cudaMemsetAsync(s.oa, 0, 8 * (size_t)B * h->cfg.T, st));
+    CUDA_TRY(h, cudaMemsetAsync(s.od, 0, 8 * (size_t)B * h->cfg.T, st));
+    CUDA_TRY(h, cudaStreamSynchronize(st));
+    return MPCB_OK;
+}
+
+int mpcb_session_set_ncourse_host(mpcb_handle* h, const int* ncourse_host) {
+    if (!h || !ncourse_host || h->ses.B <= 0) { if (h) h->err = "mpcb_session_set_ncourse_host: no session"; return MPCB_EINVAL; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    CUDA_TRY(h, cudaMemcpyAsync(h->ses.ncourse, ncourse_host, 4 * (size_t)h->ses.B, cudaMemcpyHostToDevice, h->own_stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
+    return MPCB_OK;
+}
+
+int mpcb_session_step_host(mpcb_handle* h, const double* state_host, double* di_ai_host, int* status_host) {
+    if (!h || !state_host || !di_ai_host || h->ses.B <= 0) { if (h) h->err = "mpcb_session_step_host: bad arguments / no session"; return MPCB_EINVAL; }
+    auto& s = h->ses;
+    const size_t B = (size_t)s.B;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->own_stream;
+    memcpy(s.pin + s.pin_state, state_host, 32 * B);
+    CUDA_TRY(h, cudaMemcpyAsync(s.state, s.pin + s.pin_state, 32 * B, cudaMemcpyHostToDevice, st));
+    int rc = dispatch_step(h, session_params(h), st);
+    if (rc != MPCB_OK) return rc;
+    CUDA_TRY(h, cudaMemcpyAsync(s.pin + s.pin_diai, s.di_ai, 16 * B, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(h, cudaMemcpyAsync(s.pin + s.pin_status, s.status, 4 * B, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(h, cudaStreamSynchronize(st));
+    memcpy(di_ai_host, s.pin + s.pin_diai, 16 * B);
+    if (status_host) memcpy(status_host, s.pin + s.pin_status, 4 * B);
+    return MPCB_OK;
+}
+
+int mpcb_session_step_dev(mpcb_handle* h, void* stream) {
+    if (!h || h->ses.B <= 0) { if (h) h->err = "mpcb_session_step_dev: no session"; return MPCB_EINVAL; }
+    return dispatch_step(h, session_params(h), (cudaStream_t)stream);
+}
+
+int mpcb_session_closed_loop_dev(mpcb_handle* h, int nsteps, double* history_dev, int flags, void* stream) {
+    if (!h || h->ses.B <= 0 || nsteps <= 0) { if (h) h->err = "mpcb_session_closed_loop_dev: bad arguments / no session"; return MPCB_EINVAL; }
+    auto& s = h->ses;
+    StepParams p = session_params(h);
+    p.done = s.done; p.goal = s.goal; p.state_out = s.state; p.fuse_goal = (flags & MPCB_CL_NO_GOAL_TEST) ? 0 : 1; p.fuse_plant = 1;
+    for (int k = 0; k < nsteps; ++k) {
+        p.history = history_dev ? history_dev + (size_t)k * 8 * s.B : nullptr;
+        int rc = dispatch_step(h, p, (cudaStream_t)stream);
+        if (rc != MPCB_OK) return rc;
+    }
+    return MPCB_OK;
+}
+
+void* mpcb_session_device_ptr(mpcb_handle* h, int what) {
+    if (!h || !h->ses.slab) return nullptr;
+    auto& s = h->ses;
+    switch (what) {
+        case MPCB_F_STATE: return s.state;   case MPCB_F_OA: return s.oa;         case MPCB_F_OD: return s.od;
+        case MPCB_F_TRAJ: return s.traj;     case MPCB_F_XREF: return s.xref;     case MPCB_F_DI_AI: return s.di_ai;
+        case MPCB_F_XDEV: return s.xdev;     case MPCB_F_TARGET: return s.target; case MPCB_F_WARM: return s.warm;
+        case MPCB_F_STATUS: return s.status; case MPCB_F_ITERS: return s.iters;   case MPCB_F_DONE: return s.done;
+        case MPCB_F_NCOURSE: return s.ncourse; case MPCB_F_ROUTE: return s.route; case MPCB_F_GOAL: return s.goal;
+        default: return nullptr;
+    }
+}
+
+static size_t field_bytes(const mpcb_handle* h, int what) {
+    const size_t B = (size_t)h->ses.B, T = (size_t)h->cfg.T;
+    switch (what) {
+        case MPCB_F_STATE: return 32 * B;    case MPCB_F_OA: case MPCB_F_OD: return 8 * T * B;
+        case MPCB_F_TRAJ: case MPCB_F_XREF: return 32 * (T + 1) * B;
+        case MPCB_F_DI_AI: case MPCB_F_GOAL: return 16 * B;  case MPCB_F_XDEV: return 8 * B;
+        case MPCB_F_TARGET: case MPCB_F_WARM: case MPCB_F_STATUS: case MPCB_F_ITERS: case MPCB_F_DONE:
+        case MPCB_F_NCOURSE: case MPCB_F_ROUTE: return 4 * B;
+        default: return 0;
+    }
+}
+
+long long mpcb_session_field_bytes(const mpcb_handle* h, int what) {
+    if (!h || h->ses.B <= 0) return MPCB_EINVAL;
+    return (long long)field_bytes(h, what);
+}
+
+int mpcb_session_fetch_host(mpcb_handle* h, int what, void* dst, long long bytes) {
+    if (!h || !dst || h->ses.B <= 0) { if (h) h->err = "mpcb_session_fetch_host: bad arguments / no session"; return MPCB_EINVAL; }
+    void* src = mpcb_session_device_ptr(h, what);
+    const size_t need = field_bytes(h, what);
+    if (!src || need == 0 || (size_t)bytes != need) { h->err = "mpcb_session_fetch_host: unknown field or wrong size"; return MPCB_EINVAL; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    CUDA_TRY(h, cudaMemcpyAsync(dst, src, need, cudaMemcpyDeviceToHost, h->own_stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
+    return MPCB_OK;
+}
+
+int mpcb_session_store_host(mpcb_handle* h, int what, const void* src, long long bytes) {
+    if (!h || !src || h->ses.B <= 0) { if (h) h->err = "mpcb_session_store_host: bad arguments / no session"; return MPCB_EINVAL; }
+    void* dst = mpcb_session_device_ptr(h, what);
+    const size_t need = field_bytes(h, what);
+    if (!dst || need == 0 || (size_t)bytes != need) { h->err = "mpcb_session_store_host: unknown field or wrong size"; return MPCB_EINVAL; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    CUDA_TRY(h, cudaMemcpyAsync(dst, src, need, cudaMemcpyHostToDevice, h->own_stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
+    return MPCB_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
 
 long long mpcb_launch_count(const mpcb_handle* h) { return h ? h->launches : 0; }
 

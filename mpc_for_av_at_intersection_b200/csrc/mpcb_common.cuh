@@ -24,6 +24,13 @@ struct StepParams {
     double* xdev;            // [B] out (may be null)
     int* status;             // [B] out
     int* iters;              // [B] out (may be null)
+    // closed-loop fusion (all optional): goal test before the solve, plant step and history after it
+    int* done;               // [B] io or null: != 0 -> the problem is skipped (1 = reached goal, 2 = dead)
+    const double* goal;      // [B,2] needed when fuse_goal
+    double* state_out;       // [B,4] written when fuse_plant (may alias state)
+    double* history;         // [B,8] row of this step or null: x y yaw v delta a xref_dev status
+    int fuse_goal, fuse_plant;
+    double goal_dis, stop_speed;
     // config (main/config/mpc_config.json after main/lib/mpc.py:17-36)
     double w_perp, w_para, R0, R1, Rd0, Rd1, Qv, Qyaw, Qf0, Qf1, Qf2, Qf3;   // Qf* already scaled by T
     double dsteer_dt;        // MAX_DSTEER[rad/s] * dt

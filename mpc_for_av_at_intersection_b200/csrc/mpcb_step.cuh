@@ -126,9 +126,15 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
     const double dt = p.dt;
 
     // ---- problem inputs ------------------------------------------------------------------------
+    if (p.done && p.done[b] != 0) return;
     const double x0 = p.state[4 * b + 0], y0 = p.state[4 * b + 1], yaw0 = p.state[4 * b + 2], v0 = p.state[4 * b + 3];
     const int route = p.route[b];
     const int nc = p.ncourse[b];
+    if (p.fuse_goal) {       // MPC.is_goal (main/lib/mpc.py:310-326) as the loop head of mpc_intersection.py:97
+        const double gd = hypot(x0 - p.goal[2 * b], y0 - p.goal[2 * b + 1]);
+        const bool isgoal = gd <= p.goal_dis && abs(p.target_ind[b] - nc) < 5 && fabs(v0) <= p.stop_speed;
+        if (isgoal) { if (lane == 0) p.done[b] = 1; return; }
+    }
     const double L = p.L ? p.L[b] : p.wheelbase;
     const double dl = p.dl[route];
     const double* __restrict__ cx = p.courses + (size_t)route * 3 * p.ncmax;
@@ -529,7 +535,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
 
     // ---- A7: bookkeeping of MPC.step (main/lib/mpc.py:289-299) -------------------------------------------
     if (status == MPCB_ST_NEAREST) {          // the reference raises here: nothing of the object changes
-        if (lane == 0) { p.status[b] = status; if (p.iters) p.iters[b] = 0; }
+        if (lane == 0) { p.status[b] = status; if (p.iters) p.iters[b] = 0; if (p.fuse_plant && p.done) p.done[b] = 2; }
         return;
     }
     const size_t tb = (size_t)b * 4 * (T + 1);
@@ -569,6 +575,32 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
             }
             p.xdev[b] = dev;
         }
+    }
+    if (p.fuse_plant) {
+        // Simulation.step with the applied controls (main/lib/simulation.py:35-47, main/bicycle/main.py:28-41);
+        // every lane computes the same numbers, lanes 0..7 store one history column each
+        const double di = solved ? shfl(od, 0) : p.di_ai[2 * b];
+        const double ai = solved ? shfl(oa, 0) : p.max_decel;
+        const double dcl = clampd(di, -p.max_steer, p.max_steer);
+        double sn, cs;
+        sincos(yaw0, &sn, &cs);
+        const double xd = __dmul_rn(v0, cs), yd = __dmul_rn(v0, sn);
+        const double td = __dmul_rn(__ddiv_rn(v0, L), tan(dcl));
+        const double nx = __dadd_rn(x0, __dmul_rn(xd, dt)), ny = __dadd_rn(y0, __dmul_rn(yd, dt));
+        const double nyaw = __dadd_rn(yaw0, __dmul_rn(td, dt));
+        const double nv = clampd(__dadd_rn(v0, __dmul_rn(ai, dt)), p.min_speed, p.max_speed);
+        double dev = qnan;
+        if (solved && tind < nc) {
+            const double ang = cyaw[tind] + 3.141592653589793 / 2;
+            const double ex = cos(ang) * (cx[tind] - x0), ey = sin(ang) * (cy[tind] - y0);
+            dev = sqrt(ex * ex + ey * ey);
+        }
+        double col = nx;
+        col = lane == 1 ? ny : col;  col = lane == 2 ? nyaw : col;  col = lane == 3 ? nv : col;
+        col = lane == 4 ? di : col;  col = lane == 5 ? ai : col;    col = lane == 6 ? dev : col;
+        col = lane == 7 ? (double)status : col;
+        if (lane < 4) p.state_out[4 * b + lane] = col;
+        if (p.history && lane < 8) p.history[8 * (size_t)b + lane] = col;
     }
 }
 

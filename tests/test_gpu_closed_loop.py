@@ -1,0 +1,109 @@
+"""Closed-loop parity on the GPU: the reference's own loops (main/scenarios/mpc_intersection.py:95-159 without
+obstacles; 12 routes) recorded by oracle/gen_golden.py, replayed (a) fully on the device with one fused
+launch per control step and (b) through the host-buffer session call with a host-side plant.
+
+Tolerances (BASELINE.json north_star): closed-loop positions within 1e-3 m over the rollout (asserted at 1e-4),
+applied controls within 1e-4 (asserted at 2e-5 along the loop: closed-loop differences compound), number of
+steps to goal / done flags / target indices bit-exact."""
+import numpy as np
+import pytest
+
+from conftest import golden, load_routes
+
+pytestmark = pytest.mark.gpu
+
+
+def _session(T, B):
+    from mpc_for_av_at_intersection_b200 import CourseSet, MpcConfig, MpcSession
+    cfg = MpcConfig.from_json(T=T)
+    cs = CourseSet(load_routes(False))
+    return MpcSession(cfg, cs, B), cfg, cs
+
+
+def _loops(g):
+    sel = np.flatnonzero(g["loop_obstacles"] == 0)
+    off = g["history_off"]
+    hist = [g["history"][off[i]:off[i + 1]] for i in sel]
+    return sel, g["loop_route"][sel].astype(np.int32), g["loop_len"][sel], hist
+
+
+@pytest.mark.parametrize("T", [13, 20])
+def test_device_closed_loop_matches_reference_history(T):
+    import torch
+    g = golden(f"closed_loop_T{T}.npz")
+    sel, route, nsteps, hist = _loops(g)
+    B = len(sel)
+    ses, cfg, cs = _session(T, B)
+    ses.begin(route)
+    state0 = np.stack([h[0, :4] for h in hist])
+    ses.store("state", state0)
+    K = int(nsteps.max()) + 3
+    H = torch.full((K, B, 8), float("nan"), dtype=torch.float64, device="cuda")
+    ses.closed_loop_dev(K, H.data_ptr(), 0)
+    torch.cuda.synchronize()
+    H = H.cpu().numpy()
+    done = ses.fetch("done")
+    assert np.array_equal(done, np.ones(B, np.int32)), "every loop must reach is_goal"
+    assert ses.launches == K
+    worst_p = worst_u = worst_dev = 0.0
+    for b in range(B):
+        n = int(nsteps[b])
+        rows = H[:, b]
+        valid = ~np.isnan(rows[:, 0])
+        assert valid.sum() == n and valid[:n].all(), f"loop {b}: steps to goal {valid.sum()} != reference {n}"
+        ref = hist[b][1:n + 1]           # history row k+1 is the state after control step k
+        worst_p = max(worst_p, np.abs(rows[:n, :2] - ref[:, :2]).max())
+        worst_u = max(worst_u, np.abs(rows[:n, 4:6] - ref[:, 4:6]).max())
+        worst_dev = max(worst_dev, np.nanmax(np.abs(rows[:n, 6] - ref[:, 6])))
+        assert np.abs(rows[:n, 2:4] - ref[:, 2:4]).max() < 1e-4
+        assert (rows[:n, 7] <= 1).all()
+    print(f"T={T}: {B} loops, max|dpos|={worst_p:.2e} m, max|du|={worst_u:.2e}, max|ddev|={worst_dev:.2e}")
+    assert worst_p < 1e-4 and worst_u < 2e-5 and worst_dev < 1e-4
+
+
+@pytest.mark.parametrize("T", [20])
+def test_host_session_closed_loop(T):
+    """`di, ai = mpc.step(state)` with host buffers + the caller's plant, as a scenario script would drive it."""
+    from mpc_for_av_at_intersection_b200.scenarios import host_plant_step
+    g = golden(f"closed_loop_T{T}.npz")
+    sel, route, nsteps, hist = _loops(g)
+    B = len(sel)
+    ses, cfg, cs = _session(T, B)
+    ses.begin(route)
+    state = np.stack([h[0, :4] for h in hist])
+    K = int(nsteps.min())
+    worst = 0.0
+    for k in range(K):
+        d, a = ses.step(state)
+        assert (ses.status <= 1).all()
+        ref_u = np.stack([h[k + 1, 4:6] for h in hist])
+        worst = max(worst, np.abs(d - ref_u[:, 0]).max(), np.abs(a - ref_u[:, 1]).max())
+        state = host_plant_step(state, d, a, cfg.wheelbase, cfg.dt)
+        ref_s = np.stack([h[k + 1, :4] for h in hist])
+        assert np.abs(state - ref_s).max() < 1e-4
+    # attributes a caller reads after a step (mpc.ox, mpc.xref, mpc.target_ind)
+    traj, xref, tind = ses.fetch("traj"), ses.fetch("xref"), ses.fetch("target_ind")
+    assert traj.shape == (B, 4, T + 1) and xref.shape == (B, 4, T + 1) and tind.shape == (B,)
+    assert np.isfinite(traj).all()
+    print(f"host session: {K} steps x {B} loops, max|du|={worst:.2e}")
+    assert worst < 2e-5
+
+
+def test_sharded_sweep_is_union_of_single(T=20):
+    """Config-4 property: a scenario sweep split into shards reproduces the unsplit sweep bit for bit."""
+    from mpc_for_av_at_intersection_b200.scenarios import make_workload
+    ses, cfg, cs = _session(T, 512)
+    wl = make_workload(cs, 512, seed=77)
+    ses.begin(wl["route"], target_ind=wl["target_ind"])
+    ses.store("state", wl["state"])
+    ses.closed_loop_dev(5, 0, 0, goal_test=False)
+    full = ses.fetch("state"), ses.fetch("di_ai"), ses.fetch("target_ind")
+    parts = []
+    for r in range(2):
+        w = make_workload(cs, 256, seed=77, first=256 * r)
+        ses.begin(w["route"], target_ind=w["target_ind"])
+        ses.store("state", w["state"])
+        ses.closed_loop_dev(5, 0, 0, goal_test=False)
+        parts.append((ses.fetch("state"), ses.fetch("di_ai"), ses.fetch("target_ind")))
+    for i in range(3):
+        assert np.array_equal(full[i], np.concatenate([p[i] for p in parts]))
