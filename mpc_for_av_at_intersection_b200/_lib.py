@@ -49,7 +49,8 @@ def build(verbose=False):
         [os.path.join(_HERE, "..", "include", "mpcb.h")]
     if os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):
         return LIB_PATH
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + srcs
+    extra = os.environ.get("MPCB_EXTRA_NVCC_FLAGS", "").split()
+    cmd = ["nvcc"] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + srcs
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise MpcbError("nvcc failed:\n" + res.stderr[-4000:])

@@ -34,6 +34,9 @@ struct mpcb_handle {
     HostStage stage;
     cudaStream_t own_stream = nullptr;
     int smem_optin = 0;
+    cudaStream_t last_stream = nullptr;   // stream of the last asynchronous session call (fetch/store wait on it)
+    bool last_stream_set = false;
+    int variant = 0;             // kernel tuning variant (MPCB_VARIANT, only in MPCB_TUNE_VARIANTS builds)
     int* len_dev = nullptr;
     std::vector<int> len_host;
     std::vector<double> goal_host;   // [R,2] last point of each full course (mpc.py:263)
@@ -118,13 +121,14 @@ namespace {
 
 constexpr int kHorizons[] = {10, 13, 20};
 
-template <int T, int WARPS>
+template <int T, int WARPS, int MINB>
 int launch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     const size_t smem = sizeof(mpcb::WarpSmem<T>) * WARPS;
-    auto kern = mpcb::mpc_step_kernel<T, WARPS>;
+    auto kern = mpcb::mpc_step_kernel<T, WARPS, MINB>;
     static thread_local int configured_dev = -1;
     if (configured_dev != h->device) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         configured_dev = h->device;
     }
     const int grid = (p.B + WARPS - 1) / WARPS;
@@ -133,6 +137,8 @@ int launch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     h->launches++;
     return MPCB_OK;
 }
+
+int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st);
 
 StepParams make_params(const mpcb_handle* h) {
     const mpcb_config& c = h->cfg;
@@ -199,6 +205,7 @@ int mpcb_create(const mpcb_config* cfg, int max_batch, int device, mpcb_handle**
     h->cfg = *cfg; h->device = device; h->max_batch = max_batch;
     if (cudaSetDevice(device) != cudaSuccess) { g_create_error = "cudaSetDevice failed"; delete h; return MPCB_ECUDA; }
     cudaDeviceGetAttribute(&h->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (const char* v = getenv("MPCB_VARIANT")) h->variant = atoi(v);
     if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
         g_create_error = "cudaStreamCreate failed"; delete h; return MPCB_ECUDA;
     }
@@ -269,12 +276,7 @@ int mpcb_step(mpcb_handle* h, int B, const double* state_dev, const int* route_d
     p.target_ind = target_ind_dev; p.warm = warm_dev; p.oa = oa_dev; p.od = od_dev; p.traj = traj_dev;
     p.xref = xref_dev; p.di_ai = di_ai_dev; p.xdev = xdev_dev; p.status = status_dev; p.iters = iters_dev;
     cudaStream_t st = (cudaStream_t)stream;
-    switch (h->cfg.T) {
-        case 10: return launch_step<10, 4>(h, p, st);
-        case 13: return launch_step<13, 4>(h, p, st);
-        case 20: return launch_step<20, 4>(h, p, st);
-        default: h->err = "mpcb_step: unsupported horizon"; return MPCB_EINVAL;
-    }
+    return dispatch_step(h, p, st);
 }
 
 int mpcb_plant_step(mpcb_handle* h, int B, double* state_dev, const double* di_ai_dev, const double* L_dev,
@@ -381,9 +383,18 @@ namespace {
 
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     switch (h->cfg.T) {
-        case 10: return launch_step<10, 4>(h, p, st);
-        case 13: return launch_step<13, 4>(h, p, st);
-        case 20: return launch_step<20, 4>(h, p, st);
+        case 10: return launch_step<10, 4, 4>(h, p, st);
+        case 13: return launch_step<13, 4, 4>(h, p, st);
+        case 20:
+#ifdef MPCB_TUNE_VARIANTS
+            switch (h->variant) {
+                case 1: return launch_step<20, 4, 2>(h, p, st);
+                case 2: return launch_step<20, 3, 5>(h, p, st);
+                case 3: return launch_step<20, 4, 4>(h, p, st);
+                default: break;
+            }
+#endif
+            return launch_step<20, 4, 3>(h, p, st);
         default: h->err = "mpcb: unsupported horizon"; return MPCB_EINVAL;
     }
 }
@@ -432,6 +443,7 @@ int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* 
     if (!h || B <= 0 || B > h->max_batch || !route_host) { if (h) h->err = "mpcb_session_begin: bad arguments"; return MPCB_EINVAL; }
     if (!h->courses_dev) { h->err = "mpcb_session_begin: no courses set"; return MPCB_EINVAL; }
     CUDA_TRY(h, cudaSetDevice(h->device));
+    if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
     int rc = session_alloc(h);
     if (rc != MPCB_OK) return rc;
     auto& s = h->ses;
@@ -464,6 +476,7 @@ int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* 
 int mpcb_session_set_ncourse_host(mpcb_handle* h, const int* ncourse_host) {
     if (!h || !ncourse_host || h->ses.B <= 0) { if (h) h->err = "mpcb_session_set_ncourse_host: no session"; return MPCB_EINVAL; }
     CUDA_TRY(h, cudaSetDevice(h->device));
+    if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
     CUDA_TRY(h, cudaMemcpyAsync(h->ses.ncourse, ncourse_host, 4 * (size_t)h->ses.B, cudaMemcpyHostToDevice, h->own_stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
     return MPCB_OK;
@@ -474,6 +487,7 @@ int mpcb_session_step_host(mpcb_handle* h, const double* state_host, double* di_
     auto& s = h->ses;
     const size_t B = (size_t)s.B;
     CUDA_TRY(h, cudaSetDevice(h->device));
+    if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
     cudaStream_t st = h->own_stream;
     memcpy(s.pin + s.pin_state, state_host, 32 * B);
     CUDA_TRY(h, cudaMemcpyAsync(s.state, s.pin + s.pin_state, 32 * B, cudaMemcpyHostToDevice, st));
@@ -489,12 +503,14 @@ int mpcb_session_step_host(mpcb_handle* h, const double* state_host, double* di_
 
 int mpcb_session_step_dev(mpcb_handle* h, void* stream) {
     if (!h || h->ses.B <= 0) { if (h) h->err = "mpcb_session_step_dev: no session"; return MPCB_EINVAL; }
+    h->last_stream = (cudaStream_t)stream; h->last_stream_set = true;
     return dispatch_step(h, session_params(h), (cudaStream_t)stream);
 }
 
 int mpcb_session_closed_loop_dev(mpcb_handle* h, int nsteps, double* history_dev, int flags, void* stream) {
     if (!h || h->ses.B <= 0 || nsteps <= 0) { if (h) h->err = "mpcb_session_closed_loop_dev: bad arguments / no session"; return MPCB_EINVAL; }
     auto& s = h->ses;
+    h->last_stream = (cudaStream_t)stream; h->last_stream_set = true;
     StepParams p = session_params(h);
     p.done = s.done; p.goal = s.goal; p.state_out = s.state; p.fuse_goal = (flags & MPCB_CL_NO_GOAL_TEST) ? 0 : 1; p.fuse_plant = 1;
     for (int k = 0; k < nsteps; ++k) {
@@ -541,6 +557,7 @@ int mpcb_session_fetch_host(mpcb_handle* h, int what, void* dst, long long bytes
     const size_t need = field_bytes(h, what);
     if (!src || need == 0 || (size_t)bytes != need) { h->err = "mpcb_session_fetch_host: unknown field or wrong size"; return MPCB_EINVAL; }
     CUDA_TRY(h, cudaSetDevice(h->device));
+    if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));   // order after asynchronous session work
     CUDA_TRY(h, cudaMemcpyAsync(dst, src, need, cudaMemcpyDeviceToHost, h->own_stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
     return MPCB_OK;
@@ -552,6 +569,7 @@ int mpcb_session_store_host(mpcb_handle* h, int what, const void* src, long long
     const size_t need = field_bytes(h, what);
     if (!dst || need == 0 || (size_t)bytes != need) { h->err = "mpcb_session_store_host: unknown field or wrong size"; return MPCB_EINVAL; }
     CUDA_TRY(h, cudaSetDevice(h->device));
+    if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));   // order after asynchronous session work
     CUDA_TRY(h, cudaMemcpyAsync(dst, src, need, cudaMemcpyHostToDevice, h->own_stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
     return MPCB_OK;

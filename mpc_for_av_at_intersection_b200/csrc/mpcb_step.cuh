@@ -34,12 +34,20 @@ namespace mpcb {
 template <int T>
 struct WarpSmem {
     static constexpr int N = 2 * T;
-    static constexpr int LS = 2 * T + 1;      // odd column stride: conflict-free row reads in the back solve
-    double H[3 * T][T];                        // [slot][lane]: A row | B row | C row of the cost Hessian
-    double Lc[N][LS];                          // Lc[k][i] = unscaled column k of the factor (rows i >= k)
+    static constexpr int TRI = T * (T + 1) / 2;    // packed lower triangle, column major: (i,j), i >= j, at offT(j) + i - j
+    static constexpr int LTRI = N * (N + 1) / 2;
+    double HA[TRI];                            // cost Hessian, accel block (lower)
+    double HC[TRI];                            // steer block (lower)
+    double HB[T * T];                          // cross block d/a, [col j][row lane]
+    double L[LTRI];                            // unscaled factor columns: (r,k), r >= k, at offL(k) + r - k
     double inv[N];                             // 1 / d_k
     double z[N];                               // broadcast slot of the fused forward solve
     double bc[8][T + 1];                       // per-stage broadcast tables used while assembling H
+    __host__ __device__ static constexpr int offT(int j) { return j * T - j * (j - 1) / 2; }
+    __host__ __device__ static constexpr int offL(int k) { return k * N - k * (k - 1) / 2; }
+    // lanes read/write column k at row r; consecutive lanes -> consecutive addresses (conflict free); a lane
+    // above the diagonal lands on the tail of the previous column (valid memory, value never used)
+    __device__ __forceinline__ double& Lat(int k, int r) { return L[offL(k) + r - k]; }
 };
 
 // top-3 insertion keeping (d, idx) ascending; ties keep the earlier (lower) index first
@@ -114,8 +122,8 @@ __device__ __forceinline__ void GT_apply(const double (&y)[8], double dt, int la
     gd = y[2] - y[3] - r + shfl_up1(r, lane);
 }
 
-template <int T, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParams p) {
+template <int T, int WARPS, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepParams p) {
     static_assert(T >= 3 && T <= 31, "one warp per problem needs T+1 <= 32");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -264,7 +272,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
                 const double Bij = kB * ((j <= lane) ? Blo : Bup);
                 if (j == lane) { Aij += 2.0 * ra_w + 2.0 * p.Rd0 * nb; Cij += 2.0 * rd_w + 2.0 * p.Rd1 * nb; }
                 if (j == lane - 1) { Aij -= 2.0 * p.Rd0; Cij -= 2.0 * p.Rd1; }
-                if (act) { sm.H[j][lane] = Aij; sm.H[T + j][lane] = Bij; sm.H[2 * T + j][lane] = Cij; }
+                if (act) {
+                    sm.HB[j * T + lane] = Bij;
+                    if (j <= lane) { sm.HA[WarpSmem<T>::offT(j) + lane - j] = Aij; sm.HC[WarpSmem<T>::offT(j) + lane - j] = Cij; }
+                }
             }
             __syncwarp();
         }
@@ -365,9 +376,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
                 const double dA = w[0] + w[1], dC = w[2] + w[3] + wr + wr_prev;
 #pragma unroll
                 for (int j = 0; j < T; ++j) {
-                    A[j] = (act ? sm.H[j][lane] : 0.0) + wv_suf + (j == lane ? dA : 0.0);
-                    Bm[j] = act ? sm.H[T + j][lane] : 0.0;
-                    C[j] = (act ? sm.H[2 * T + j][lane] : 0.0) + (j == lane ? dC : 0.0) - (j == lane - 1 ? wr_prev : 0.0);
+                    A[j] = (act ? sm.HA[WarpSmem<T>::offT(j) + lane - j] : 0.0) + wv_suf + (j == lane ? dA : 0.0);
+                    Bm[j] = act ? sm.HB[j * T + lane] : 0.0;
+                    C[j] = (act ? sm.HC[WarpSmem<T>::offT(j) + lane - j] : 0.0) + (j == lane ? dC : 0.0) - (j == lane - 1 ? wr_prev : 0.0);
                 }
             }
             // affine right-hand side: -r_d + G'(lam - W r_p)
@@ -383,8 +394,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
             bool bad = false;
 #pragma unroll
             for (int k = 0; k < T; ++k) {
-                if (act && lane >= k) sm.Lc[k][lane] = A[k];
-                if (act) sm.Lc[k][T + lane] = Bm[k];
+                if (act && lane >= k) sm.Lat(k, lane) = A[k];
+                if (act) sm.Lat(k, T + lane) = Bm[k];
                 if (lane == k) {
                     bad = bad || !(A[k] > 0.0);
                     sm.inv[k] = rcp(A[k]);
@@ -398,16 +409,16 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
                 rdl -= Bm[k] * zk;
 #pragma unroll
                 for (int j = k + 1; j < T; ++j) {
-                    const double cj = sm.Lc[k][j];
+                    const double cj = sm.Lat(k, j);
                     A[j] -= la * cj;
                     Bm[j] -= lb * cj;
                 }
 #pragma unroll
-                for (int j = 0; j < T; ++j) C[j] -= lb * sm.Lc[k][T + j];
+                for (int j = 0; j < T; ++j) C[j] -= lb * sm.Lat(k, T + j);
             }
 #pragma unroll
             for (int k = 0; k < T; ++k) {
-                if (act && lane >= k) sm.Lc[T + k][T + lane] = C[k];
+                if (act && lane >= k) sm.Lat(T + k, T + lane) = C[k];
                 if (lane == k) {
                     bad = bad || !(C[k] > 0.0);
                     sm.inv[T + k] = rcp(C[k]);
@@ -419,7 +430,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
                 const double lc = C[k] * iv;
                 if (lane > k) rdl -= C[k] * zk;
 #pragma unroll
-                for (int j = k + 1; j < T; ++j) C[j] -= lc * sm.Lc[T + k][T + j];
+                for (int j = k + 1; j < T; ++j) C[j] -= lc * sm.Lat(T + k, T + j);
             }
             if (__any_sync(MPCB_FULL, bad)) { broke = true; break; }
             const double inva = act ? sm.inv[lane] : 0.0, invd = act ? sm.inv[T + lane] : 0.0;
@@ -434,15 +445,15 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
                     const double xk = shfl(wd - invd * accD, k);
                     if (lane == k) xd = xk;
                     if (act) {
-                        if (lane < k) accD += sm.Lc[T + lane][T + k] * xk;
-                        accA += sm.Lc[lane][T + k] * xk;
+                        if (lane < k) accD += sm.Lat(T + lane, T + k) * xk;
+                        accA += sm.Lat(lane, T + k) * xk;
                     }
                 }
 #pragma unroll
                 for (int k = T - 1; k >= 0; --k) {
                     const double xk = shfl(wa - inva * accA, k);
                     if (lane == k) xa = xk;
-                    if (act && lane < k) accA += sm.Lc[lane][k] * xk;
+                    if (act && lane < k) accA += sm.Lat(lane, k) * xk;
                 }
             };
             auto fwd_solve = [&](double& fa, double& fd) {     // L z = r, factor read from shared memory
@@ -450,14 +461,14 @@ __global__ void __launch_bounds__(WARPS * 32, 1) mpc_step_kernel(const StepParam
                 for (int k = 0; k < T; ++k) {
                     const double zk = shfl(fa, k) * sm.inv[k];
                     if (act) {
-                        if (lane > k) fa -= sm.Lc[k][lane] * zk;
-                        fd -= sm.Lc[k][T + lane] * zk;
+                        if (lane > k) fa -= sm.Lat(k, lane) * zk;
+                        fd -= sm.Lat(k, T + lane) * zk;
                     }
                 }
 #pragma unroll
                 for (int k = 0; k < T; ++k) {
                     const double zk = shfl(fd, k) * sm.inv[T + k];
-                    if (act && lane > k) fd -= sm.Lc[T + k][T + lane] * zk;
+                    if (act && lane > k) fd -= sm.Lat(T + k, T + lane) * zk;
                 }
             };
 
