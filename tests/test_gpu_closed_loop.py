@@ -117,3 +117,19 @@ def test_sharded_sweep_is_union_of_single(T=20):
         parts.append((ses.fetch("state"), ses.fetch("di_ai"), ses.fetch("target_ind")))
     for i in range(3):
         assert np.array_equal(full[i], np.concatenate([p[i] for p in parts]))
+
+
+def test_closed_loop_sweep_chunks_and_shards():
+    """run_closed_loop_sweep: chunked processing and a 2-way shard give the same per-scenario results as one pass."""
+    from mpc_for_av_at_intersection_b200 import CourseSet, MpcConfig
+    from mpc_for_av_at_intersection_b200.sweep import run_closed_loop_sweep
+    cfg = MpcConfig.from_json(T=20)
+    cs = CourseSet(load_routes(False))
+    one = run_closed_loop_sweep(cfg, cs, 300, 12, seed=3, chunk=4096, keep_history=True)
+    chunked = run_closed_loop_sweep(cfg, cs, 300, 12, seed=3, chunk=128)
+    halves = [run_closed_loop_sweep(cfg, cs, 300, 12, seed=3, rank=r, world=2) for r in range(2)]
+    for k in ("steps_to_goal", "final_state", "fail_count"):
+        assert np.array_equal(one[k], chunked[k]), k
+        assert np.array_equal(one[k], np.concatenate([h[k] for h in halves])), k
+    assert one["history"].shape == (300, 12, 8) and (one["fail_count"] == 0).all()
+    assert np.isfinite(one["final_state"]).all()
