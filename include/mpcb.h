@@ -70,6 +70,12 @@ typedef struct mpcb_config {
     double ipm_tol_mu;     /* complementarity gap target, default 1e-12                      */
     double ipm_tol_p;      /* primal residual,             default 1e-10                     */
     double ipm_tol_d;      /* dual residual (absolute part), default 1e-9                    */
+    /* inter-vehicle coupling (row A9): CarDimensions.bounding_box_size (main/lib/car_dimensions.py:82-107) and the
+     * literals of main/scenarios/mpc_intersection.py:81-84 */
+    double car_width;      /* 2.0 (bicycle model) / 2.04 s (Prius): circle radius = width / sqrt(2)  */
+    double car_length;     /* wheelbase + 0.64 = 3.5 / 4.84 s                                        */
+    double coupling_horizon; /* TIME_HORIZON = 7.0 s -> 35 predicted obstacle frames at dt = 0.2       */
+    int frame_window;      /* FRAME_WINDOW = 20: obstacle trajectories are time-shifted by -20..+20 frames */
 } mpcb_config;
 
 typedef struct mpcb_handle mpcb_handle;
@@ -180,6 +186,46 @@ void* mpcb_session_device_ptr(mpcb_handle* h, int what);
 long long mpcb_session_field_bytes(const mpcb_handle* h, int what);
 int mpcb_session_fetch_host(mpcb_handle* h, int what, void* dst, long long bytes);
 int mpcb_session_store_host(mpcb_handle* h, int what, const void* src, long long bytes);
+
+/* ---- inter-vehicle coupling (row A9) ---------------------------------------------------------------
+ * replaces, per ego vehicle and control step, main/scenarios/mpc_intersection.py:100-139:
+ * calc_nearest_index_in_direction on the full path -> resample_curve ego prediction
+ * (main/lib/trajectories.py:58-86) -> MovingObstaclesPrediction.state_prediction
+ * (main/lib/moving_obstacles_prediction.py:21-47) -> check_collision_moving_cars
+ * (main/lib/collision_avoidance.py:66-104) -> get_cutoff_curve_by_position_idx (:107-119) -> cutoff_idx.
+ *   state_dev     [B,4]  x, y, yaw, v of every ego
+ *   route_dev     [B]
+ *   obs_dev       [B,MPCB_MAX_OBSTACLES,6] obstacle states in MovingObstacle*.get() order (x, y, v, yaw, a, steer);
+ *                 ignored (may be NULL) when vehicles_per_scenario > 0
+ *   n_obs_dev     [B]    obstacles per ego (<= MPCB_MAX_OBSTACLES), NULL = 0
+ *   done_dev      [B] or NULL: finished egos are skipped (their cut is kept)
+ *   agent_idx_dev [B]    in/out  traj_agent_idx
+ *   ncourse_dev   [B]    in/out  in: len(tmp_trajectory) of the previous step (0 = None), out: new cutoff_idx
+ *                        (= the full course length when nothing collides) -- feed it to mpcb_step as ncourse
+ *   collided_dev  [B] out (0/1), coll_idx_dev [B] out (index into full[agent_idx:], -1), coll_xy_dev [B,2] out,
+ *   n_res_dev     [B] out len(trajectory_res), flags_dev [B] out (bit0 nearest-index exception, bit1 overflow);
+ *                 any of the five may be NULL
+ *   vehicles_per_scenario  > 0: problems are grouped in scenarios of that many consecutive egos and every ego takes
+ *                 the OTHER egos of its scenario as obstacles (constant speed, zero steer: the intent stated at
+ *                 main/scenarios/interactive_mpc_temp.py:168); all egos read start-of-step states (Jacobi order,
+ *                 ibid.:124-210).  0: obstacles come from obs_dev. */
+#define MPCB_MAX_OBSTACLES 8
+int mpcb_coupling(mpcb_handle* h, int B, const double* state_dev, const int* route_dev, const double* obs_dev,
+                  const int* n_obs_dev, const int* done_dev, int* agent_idx_dev, int* ncourse_dev, int* collided_dev,
+                  int* coll_idx_dev, double* coll_xy_dev, int* n_res_dev, int* flags_dev, int vehicles_per_scenario,
+                  void* stream);
+/* same with HOST buffers (synchronous); in/out arrays are updated in place */
+int mpcb_coupling_host(mpcb_handle* h, int B, const double* state, const int* route, const double* obs,
+                       const int* n_obs, int* agent_idx, int* ncourse, int* collided, int* coll_idx, double* coll_xy,
+                       int* n_res, int* flags, int vehicles_per_scenario);
+/* replaces: the multi-vehicle closed loop (SURVEY.md section 8a, A9 spec; main/scenarios/interactive_mpc_temp.py:124-210
+ * as intended): nsteps x (is_goal | coupling against the other egos of the scenario | mpc.step | simulation.step),
+ * two kernel launches per control step on the resident session.  history_dev as mpcb_session_closed_loop_dev. */
+int mpcb_session_multi_agent_dev(mpcb_handle* h, int nsteps, int vehicles_per_scenario, double* history_dev, int flags,
+                                 void* stream);
+#define MPCB_F_AGENT_IDX 15 /* int [B] traj_agent_idx */
+#define MPCB_F_COLLIDED 16  /* int [B] */
+#define MPCB_F_COLL_IDX 17  /* int [B] */
 
 /* kernels launched by this handle so far (bench.py's gpu_launches) */
 long long mpcb_launch_count(const mpcb_handle* h);

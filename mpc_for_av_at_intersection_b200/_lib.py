@@ -26,6 +26,8 @@ class mpcb_config(C.Structure):
         ("min_ref_speed", C.c_double), ("dt", C.c_double), ("wheelbase", C.c_double),
         ("ipm_max_iter", C.c_int), ("ipm_tol_mu", C.c_double), ("ipm_tol_p", C.c_double),
         ("ipm_tol_d", C.c_double),
+        ("car_width", C.c_double), ("car_length", C.c_double), ("coupling_horizon", C.c_double),
+        ("frame_window", C.c_int),
     ]
 
 
@@ -36,10 +38,12 @@ EXPORTS = [
     "mpcb_session_begin", "mpcb_session_set_ncourse_host", "mpcb_session_step_host", "mpcb_session_step_dev",
     "mpcb_session_closed_loop_dev", "mpcb_session_device_ptr", "mpcb_session_field_bytes",
     "mpcb_session_fetch_host", "mpcb_session_store_host",
+    "mpcb_coupling", "mpcb_coupling_host", "mpcb_session_multi_agent_dev",
 ]
 
 F_STATE, F_OA, F_OD, F_TRAJ, F_XREF, F_DI_AI, F_XDEV, F_TARGET, F_WARM, F_STATUS, F_ITERS, F_DONE, F_NCOURSE, \
-    F_ROUTE, F_GOAL = range(15)
+    F_ROUTE, F_GOAL, F_AGENT_IDX, F_COLLIDED, F_COLL_IDX = range(18)
+MAX_OBSTACLES = 8
 
 
 def build(verbose=False):
@@ -113,6 +117,12 @@ def lib():
     L.mpcb_session_fetch_host.restype = C.c_int
     L.mpcb_session_store_host.argtypes = [vp, C.c_int, vp, C.c_longlong]
     L.mpcb_session_store_host.restype = C.c_int
+    L.mpcb_coupling.argtypes = [vp, C.c_int] + [vp] * 12 + [C.c_int, vp]
+    L.mpcb_coupling.restype = C.c_int
+    L.mpcb_coupling_host.argtypes = [vp, C.c_int] + [vp] * 11 + [C.c_int]
+    L.mpcb_coupling_host.restype = C.c_int
+    L.mpcb_session_multi_agent_dev.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, vp]
+    L.mpcb_session_multi_agent_dev.restype = C.c_int
     L.mpcb_launch_count.argtypes = [vp]
     L.mpcb_launch_count.restype = C.c_longlong
     L.mpcb_measure_fp64_peak.argtypes = [C.c_int, dp]

@@ -36,6 +36,11 @@ class MpcConfig:
     ipm_tol_mu: float = 1e-12
     ipm_tol_p: float = 1e-10
     ipm_tol_d: float = 1e-9
+    # inter-vehicle coupling (row A9): car box (car_dimensions.py:82-107) and mpc_intersection.py:81-84 literals
+    car_width: float = 2.0
+    car_length: float = 3.5
+    coupling_horizon: float = 7.0
+    frame_window: int = 20
 
     @staticmethod
     def from_json(path=None, **overrides):
@@ -67,4 +72,6 @@ class MpcConfig:
         c.dt, c.wheelbase = float(self.dt), float(self.wheelbase)
         c.ipm_max_iter = int(self.ipm_max_iter)
         c.ipm_tol_mu, c.ipm_tol_p, c.ipm_tol_d = float(self.ipm_tol_mu), float(self.ipm_tol_p), float(self.ipm_tol_d)
+        c.car_width, c.car_length = float(self.car_width), float(self.car_length)
+        c.coupling_horizon, c.frame_window = float(self.coupling_horizon), int(self.frame_window)
         return c

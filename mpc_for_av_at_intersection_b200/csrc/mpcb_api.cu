@@ -8,6 +8,7 @@
 
 #include "../../include/mpcb.h"
 #include "mpcb_step.cuh"
+#include "mpcb_coupling.cuh"
 
 namespace {
 
@@ -38,6 +39,7 @@ struct mpcb_handle {
     bool last_stream_set = false;
     int variant = 0;             // kernel tuning variant (MPCB_VARIANT, only in MPCB_TUNE_VARIANTS builds)
     int* len_dev = nullptr;
+    double* pathcc_dev = nullptr;    // [R][2 circles][x|y][ncmax]
     std::vector<int> len_host;
     std::vector<double> goal_host;   // [R,2] last point of each full course (mpc.py:263)
     // resident session: the [B,...] mirror of the reference's MPC object state lives on the device
@@ -48,7 +50,7 @@ struct mpcb_handle {
         double *state = nullptr, *L = nullptr, *oa = nullptr, *od = nullptr, *traj = nullptr, *xref = nullptr,
                *di_ai = nullptr, *xdev = nullptr, *goal = nullptr;
         int *route = nullptr, *ncourse = nullptr, *target = nullptr, *warm = nullptr, *status = nullptr,
-            *iters = nullptr, *done = nullptr;
+            *iters = nullptr, *done = nullptr, *agent_idx = nullptr, *collided = nullptr, *coll_idx = nullptr;
         bool hasL = false;
         size_t pin_state = 0, pin_diai = 0, pin_status = 0, pin_total = 0;
     } ses;
@@ -174,6 +176,8 @@ void mpcb_default_config(mpcb_config* c) {
     c->max_speed = 30.0 / 3.6; c->min_speed = -5.0; c->r_end = 10.0; c->min_ref_speed = 10 / 3.6;
     c->dt = 0.2; c->wheelbase = 2.86;
     c->ipm_max_iter = 40; c->ipm_tol_mu = 1e-12; c->ipm_tol_p = 1e-10; c->ipm_tol_d = 1e-9;
+    c->car_width = 2.0; c->car_length = 2.86 + 0.64;      // BicycleModelDimensions (car_dimensions.py:82-90)
+    c->coupling_horizon = 7.0; c->frame_window = 20;      // mpc_intersection.py:81-82
 }
 
 int mpcb_device_count(void) {
@@ -219,6 +223,7 @@ void mpcb_destroy(mpcb_handle* h) {
     if (h->courses_dev) cudaFree(h->courses_dev);
     if (h->dl_dev) cudaFree(h->dl_dev);
     if (h->len_dev) cudaFree(h->len_dev);
+    if (h->pathcc_dev) cudaFree(h->pathcc_dev);
     if (h->ses.slab) cudaFree(h->ses.slab);
     if (h->ses.pin) cudaFreeHost(h->ses.pin);
     if (h->stage.pinned) cudaFreeHost(h->stage.pinned);
@@ -258,6 +263,24 @@ int mpcb_set_courses_host(mpcb_handle* h, const double* courses_host, const int*
         const double* c = courses_host + (size_t)r * 3 * ncmax;
         h->goal_host[2 * r] = c[len_host[r] - 1];
         h->goal_host[2 * r + 1] = c[ncmax + len_host[r] - 1];
+    }
+    // circle centres of every path point (main/lib/trajectories.py:11-55, y offset 0), host libm like numpy
+    {
+        const mpcb_config& c = h->cfg;
+        const double along = c.car_length / 2 - c.car_width / 2, mid = c.wheelbase / 2;   // car_dimensions.py:59-79
+        const double offs[2] = {mid + along, mid - along};
+        std::vector<double> cc((size_t)R * 4 * ncmax);
+        for (int r = 0; r < R; ++r) {
+            const double* x = courses_host + (size_t)r * 3 * ncmax, *y = x + ncmax, *th = y + ncmax;
+            for (int k = 0; k < 2; ++k)
+                for (int i = 0; i < ncmax; ++i) {
+                    cc[((size_t)r * 4 + 2 * k) * ncmax + i] = (cos(th[i]) * offs[k] - sin(th[i]) * 0.0) + x[i];
+                    cc[((size_t)r * 4 + 2 * k + 1) * ncmax + i] = (sin(th[i]) * offs[k] + cos(th[i]) * 0.0) + y[i];
+                }
+        }
+        if (h->pathcc_dev) { cudaFree(h->pathcc_dev); h->pathcc_dev = nullptr; }
+        CUDA_TRY(h, cudaMalloc(&h->pathcc_dev, cc.size() * sizeof(double)));
+        CUDA_TRY(h, cudaMemcpy(h->pathcc_dev, cc.data(), cc.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
     h->R = R; h->ncmax = ncmax;
     return MPCB_OK;
@@ -383,18 +406,18 @@ namespace {
 
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     switch (h->cfg.T) {
-        case 10: return launch_step<10, 4, 4>(h, p, st);
-        case 13: return launch_step<13, 4, 4>(h, p, st);
+        case 10: return launch_step<10, 4, 3>(h, p, st);
+        case 13: return launch_step<13, 4, 3>(h, p, st);
         case 20:
 #ifdef MPCB_TUNE_VARIANTS
             switch (h->variant) {
-                case 1: return launch_step<20, 4, 2>(h, p, st);
+                case 1: return launch_step<20, 4, 3>(h, p, st);
                 case 2: return launch_step<20, 3, 5>(h, p, st);
                 case 3: return launch_step<20, 4, 4>(h, p, st);
                 default: break;
             }
 #endif
-            return launch_step<20, 4, 3>(h, p, st);
+            return launch_step<20, 4, 2>(h, p, st);
         default: h->err = "mpcb: unsupported horizon"; return MPCB_EINVAL;
     }
 }
@@ -409,7 +432,7 @@ int session_alloc(mpcb_handle* h) {
                  o_traj = put(8 * 4 * (T + 1) * B), o_xref = put(8 * 4 * (T + 1) * B), o_diai = put(8 * 2 * B),
                  o_xdev = put(8 * B), o_goal = put(8 * 2 * B), o_route = put(4 * B), o_nc = put(4 * B),
                  o_tgt = put(4 * B), o_warm = put(4 * B), o_status = put(4 * B), o_iters = put(4 * B),
-                 o_done = put(4 * B);
+                 o_done = put(4 * B), o_aidx = put(4 * B), o_coll = put(4 * B), o_cidx = put(4 * B);
     CUDA_TRY(h, cudaMalloc(&s.slab, o));
     CUDA_TRY(h, cudaMemset(s.slab, 0, o));
     char* d = s.slab;
@@ -418,6 +441,7 @@ int session_alloc(mpcb_handle* h) {
     s.xdev = (double*)(d + o_xdev); s.goal = (double*)(d + o_goal); s.route = (int*)(d + o_route);
     s.ncourse = (int*)(d + o_nc); s.target = (int*)(d + o_tgt); s.warm = (int*)(d + o_warm);
     s.status = (int*)(d + o_status); s.iters = (int*)(d + o_iters); s.done = (int*)(d + o_done);
+    s.agent_idx = (int*)(d + o_aidx); s.collided = (int*)(d + o_coll); s.coll_idx = (int*)(d + o_cidx);
     o = 0;
     s.pin_state = put(8 * 4 * B); s.pin_diai = put(8 * 2 * B); s.pin_status = put(4 * B);
     s.pin_total = o;
@@ -466,6 +490,9 @@ int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* 
     else CUDA_TRY(h, cudaMemsetAsync(s.target, 0, 4 * (size_t)B, st));
     CUDA_TRY(h, cudaMemsetAsync(s.warm, 0, 4 * (size_t)B, st));         // oa = odelta = None (mpc.py:265-266)
     CUDA_TRY(h, cudaMemsetAsync(s.done, 0, 4 * (size_t)B, st));
+    CUDA_TRY(h, cudaMemsetAsync(s.agent_idx, 0, 4 * (size_t)B, st));       // traj_agent_idx = 0 (mpc_intersection.py:78)
+    CUDA_TRY(h, cudaMemsetAsync(s.collided, 0, 4 * (size_t)B, st));
+    CUDA_TRY(h, cudaMemsetAsync(s.coll_idx, 0xff, 4 * (size_t)B, st));
     CUDA_TRY(h, cudaMemsetAsync(s.di_ai, 0, 16 * (size_t)B, st));       // di = ai = 0.0 (mpc.py:270-271)
     CUDA_TRY(h, cudaMemsetAsync(s.oa, 0, 8 * (size_t)B * h->cfg.T, st));
     CUDA_TRY(h, cudaMemsetAsync(s.od, 0, 8 * (size_t)B * h->cfg.T, st));
@@ -530,6 +557,7 @@ void* mpcb_session_device_ptr(mpcb_handle* h, int what) {
         case MPCB_F_XDEV: return s.xdev;     case MPCB_F_TARGET: return s.target; case MPCB_F_WARM: return s.warm;
         case MPCB_F_STATUS: return s.status; case MPCB_F_ITERS: return s.iters;   case MPCB_F_DONE: return s.done;
         case MPCB_F_NCOURSE: return s.ncourse; case MPCB_F_ROUTE: return s.route; case MPCB_F_GOAL: return s.goal;
+        case MPCB_F_AGENT_IDX: return s.agent_idx; case MPCB_F_COLLIDED: return s.collided; case MPCB_F_COLL_IDX: return s.coll_idx;
         default: return nullptr;
     }
 }
@@ -541,7 +569,7 @@ static size_t field_bytes(const mpcb_handle* h, int what) {
         case MPCB_F_TRAJ: case MPCB_F_XREF: return 32 * (T + 1) * B;
         case MPCB_F_DI_AI: case MPCB_F_GOAL: return 16 * B;  case MPCB_F_XDEV: return 8 * B;
         case MPCB_F_TARGET: case MPCB_F_WARM: case MPCB_F_STATUS: case MPCB_F_ITERS: case MPCB_F_DONE:
-        case MPCB_F_NCOURSE: case MPCB_F_ROUTE: return 4 * B;
+        case MPCB_F_NCOURSE: case MPCB_F_ROUTE: case MPCB_F_AGENT_IDX: case MPCB_F_COLLIDED: case MPCB_F_COLL_IDX: return 4 * B;
         default: return 0;
     }
 }
@@ -572,6 +600,118 @@ int mpcb_session_store_host(mpcb_handle* h, int what, const void* src, long long
     if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));   // order after asynchronous session work
     CUDA_TRY(h, cudaMemcpyAsync(dst, src, need, cudaMemcpyHostToDevice, h->own_stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
+    return MPCB_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// row A9: inter-vehicle coupling
+// ---------------------------------------------------------------------------------------------------
+namespace {
+int launch_coupling(mpcb_handle* h, CouplingParams& p, cudaStream_t st) {
+    const mpcb_config& c = h->cfg;
+    p.ncmax = h->ncmax; p.courses = h->courses_dev; p.pathcc = h->pathcc_dev; p.course_len = h->len_dev; p.dl = h->dl_dev;
+    const double along = c.car_length / 2 - c.car_width / 2, mid = c.wheelbase / 2;
+    p.circ[0] = mid + along; p.circ[1] = mid - along;
+    p.radius = c.car_width / sqrt(2.0);                          // width / 2**.5 (car_dimensions.py:64-65)
+    p.wheelbase = c.wheelbase; p.dt = c.dt; p.max_accel = c.max_accel; p.max_speed = c.max_speed;
+    p.frame_window = c.frame_window;
+    p.n_frames = (int)ceil(c.coupling_horizon / c.dt);           // len(np.arange(0, horizon, dt))
+    if (p.n_frames < 1 || p.n_frames > MPCB_CP_FRAMES || p.frame_window < 0 || p.frame_window > 64) {
+        h->err = "mpcb_coupling: coupling_horizon/dt must give 1..35 frames and frame_window 0..64"; return MPCB_EINVAL;
+    }
+    constexpr int WARPS = 4;
+    const size_t smem = sizeof(mpcb::CouplingSmem) * WARPS;
+    auto kern = mpcb::coupling_kernel<WARPS>;
+    static thread_local int configured_dev = -1;
+    if (configured_dev != h->device) {
+        CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured_dev = h->device;
+    }
+    kern<<<(p.B + WARPS - 1) / WARPS, WARPS * 32, smem, st>>>(p);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches++;
+    return MPCB_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int mpcb_coupling(mpcb_handle* h, int B, const double* state_dev, const int* route_dev, const double* obs_dev,
+                  const int* n_obs_dev, const int* done_dev, int* agent_idx_dev, int* ncourse_dev, int* collided_dev,
+                  int* coll_idx_dev, double* coll_xy_dev, int* n_res_dev, int* flags_dev, int vehicles_per_scenario,
+                  void* stream) {
+    if (!h) return MPCB_EINVAL;
+    if (B <= 0 || !state_dev || !route_dev || !agent_idx_dev || !ncourse_dev) { h->err = "mpcb_coupling: bad arguments"; return MPCB_EINVAL; }
+    if (!h->courses_dev) { h->err = "mpcb_coupling: no courses set"; return MPCB_EINVAL; }
+    if (vehicles_per_scenario < 0 || vehicles_per_scenario > MPCB_CP_MAX_OBS + 1 ||
+        (vehicles_per_scenario > 0 && B % vehicles_per_scenario != 0)) {
+        h->err = "mpcb_coupling: vehicles_per_scenario must be 0..9 and divide B"; return MPCB_EINVAL;
+    }
+    if (vehicles_per_scenario == 0 && n_obs_dev && !obs_dev) { h->err = "mpcb_coupling: n_obs without obs"; return MPCB_EINVAL; }
+    CouplingParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.vehicles_per_scenario = vehicles_per_scenario; p.state = state_dev; p.route = route_dev; p.obs = obs_dev;
+    p.n_obs = n_obs_dev; p.done = done_dev; p.agent_idx = agent_idx_dev; p.ncourse = ncourse_dev; p.collided = collided_dev;
+    p.coll_idx = coll_idx_dev; p.coll_xy = coll_xy_dev; p.n_res = n_res_dev; p.flags = flags_dev;
+    return launch_coupling(h, p, (cudaStream_t)stream);
+}
+
+int mpcb_coupling_host(mpcb_handle* h, int B, const double* state, const int* route, const double* obs,
+                       const int* n_obs, int* agent_idx, int* ncourse, int* collided, int* coll_idx, double* coll_xy,
+                       int* n_res, int* flags, int vehicles_per_scenario) {
+    if (!h) return MPCB_EINVAL;
+    if (B <= 0 || !state || !route || !agent_idx || !ncourse) { h->err = "mpcb_coupling_host: bad arguments"; return MPCB_EINVAL; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    const size_t nB = (size_t)B;
+    size_t o = 0;
+    auto put = [&](size_t bytes) { size_t at = o; o = align256(o + bytes); return at; };
+    const size_t o_state = put(32 * nB), o_route = put(4 * nB), o_obs = put(8 * 6 * MPCB_CP_MAX_OBS * nB), o_nobs = put(4 * nB),
+                 o_aidx = put(4 * nB), o_nc = put(4 * nB), o_coll = put(4 * nB), o_cidx = put(4 * nB), o_cxy = put(16 * nB),
+                 o_nres = put(4 * nB), o_flags = put(4 * nB);
+    char* d = nullptr;
+    CUDA_TRY(h, cudaMalloc(&d, o));
+    cudaStream_t st = h->own_stream;
+    int rc = MPCB_OK;
+    auto up = [&](size_t off, const void* src, size_t bytes) { if (src && cudaMemcpyAsync(d + off, src, bytes, cudaMemcpyHostToDevice, st) != cudaSuccess) rc = MPCB_ECUDA; };
+    up(o_state, state, 32 * nB); up(o_route, route, 4 * nB); up(o_obs, obs, 8 * 6 * MPCB_CP_MAX_OBS * nB);
+    up(o_nobs, n_obs, 4 * nB); up(o_aidx, agent_idx, 4 * nB); up(o_nc, ncourse, 4 * nB);
+    cudaMemsetAsync(d + o_flags, 0, 4 * nB, st);
+    if (rc == MPCB_OK)
+        rc = mpcb_coupling(h, B, (double*)(d + o_state), (int*)(d + o_route), obs ? (double*)(d + o_obs) : nullptr,
+                           n_obs ? (int*)(d + o_nobs) : nullptr, nullptr, (int*)(d + o_aidx), (int*)(d + o_nc),
+                           (int*)(d + o_coll), (int*)(d + o_cidx), (double*)(d + o_cxy), (int*)(d + o_nres),
+                           (int*)(d + o_flags), vehicles_per_scenario, st);
+    auto down = [&](void* dst, size_t off, size_t bytes) { if (dst && rc == MPCB_OK && cudaMemcpyAsync(dst, d + off, bytes, cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = MPCB_ECUDA; };
+    down(agent_idx, o_aidx, 4 * nB); down(ncourse, o_nc, 4 * nB); down(collided, o_coll, 4 * nB); down(coll_idx, o_cidx, 4 * nB);
+    down(coll_xy, o_cxy, 16 * nB); down(n_res, o_nres, 4 * nB); down(flags, o_flags, 4 * nB);
+    if (cudaStreamSynchronize(st) != cudaSuccess && rc == MPCB_OK) { h->err = "mpcb_coupling_host: CUDA failure"; rc = MPCB_ECUDA; }
+    cudaFree(d);
+    return rc;
+}
+
+int mpcb_session_multi_agent_dev(mpcb_handle* h, int nsteps, int vehicles_per_scenario, double* history_dev, int flags,
+                                 void* stream) {
+    if (!h || h->ses.B <= 0 || nsteps <= 0 || vehicles_per_scenario < 1) { if (h) h->err = "mpcb_session_multi_agent_dev: bad arguments / no session"; return MPCB_EINVAL; }
+    auto& s = h->ses;
+    h->last_stream = (cudaStream_t)stream; h->last_stream_set = true;
+    StepParams p = session_params(h);
+    p.done = s.done; p.goal = s.goal; p.state_out = s.state; p.fuse_goal = (flags & MPCB_CL_NO_GOAL_TEST) ? 0 : 1; p.fuse_plant = 1;
+    for (int k = 0; k < nsteps; ++k) {
+        // egos that already satisfy is_goal must not be re-planned: the step kernel sets done at its head, the
+        // coupling kernel of the NEXT step skips them; all egos read start-of-step states (Jacobi order)
+        int rc = mpcb_coupling(h, s.B, s.state, s.route, nullptr, nullptr, s.done, s.agent_idx, s.ncourse, s.collided,
+                               s.coll_idx, nullptr, nullptr, nullptr, vehicles_per_scenario, stream);
+        if (rc != MPCB_OK) return rc;
+        p.history = history_dev ? history_dev + (size_t)k * 8 * s.B : nullptr;
+        rc = dispatch_step(h, p, (cudaStream_t)stream);
+        if (rc != MPCB_OK) return rc;
+    }
     return MPCB_OK;
 }
 

@@ -1,0 +1,239 @@
+// mpcb_coupling.cuh -- row A9: inter-vehicle coupling, one warp per ego vehicle.
+//
+// Replaces, per ego and control step, the part of the reference loop body that decides how far the planned
+// path may be followed (main/scenarios/mpc_intersection.py:100-139):
+//   1. traj_agent_idx <- calc_nearest_index_in_direction on the FULL path      mpc_intersection.py:103-105
+//   2. ego "max-accel" prediction = resample_curve(full[idx:], dl_k)            :110-116, lib/trajectories.py:58-86
+//   3. constant-input prediction of every obstacle, 35 frames                    lib/moving_obstacles_prediction.py:21-47
+//   4. check_collision_moving_cars: circle pairs over +-frame_window offsets     lib/collision_avoidance.py:66-104
+//   5. cutoff_idx = max(idx+1, first_index_within_1mm - margin)                  :129-136, collision_avoidance.py:107-119
+// Outputs are integers/flags (bit-exact class).  Comparisons use the reference's float64 operation order
+// (norm = sqrt(dx*dx + dy*dy), no FMA contraction); cumulative sums are sequential like np.cumsum.
+#pragma once
+#include "mpcb_common.cuh"
+
+#define MPCB_CP_MAX_OBS 8          // obstacles per ego (config 3: 7 other vehicles)
+#define MPCB_CP_FRAMES 35          // len(np.arange(0, 7.0, 0.2))
+#define MPCB_CP_MAX_RES 128        // resampled ego frames kept (spacing >= 0.4 m: 60 m path -> < 64)
+
+struct CouplingParams {
+    int B, ncmax, vehicles_per_scenario;   // vehicles_per_scenario > 0: obstacles = the other egos of the scenario
+    const double* courses;       // [R][3][ncmax]
+    const double* pathcc;        // [R][2 circles][2 (x|y)][ncmax] circle centres of every path point (host-computed)
+    const int* course_len;       // [R]
+    const double* dl;            // [R]
+    const double* state;         // [B,4] x y yaw v
+    const int* route;            // [B]
+    const double* obs;           // [B, MPCB_CP_MAX_OBS, 6] x y v yaw a steer (MovingObstacle*.get()), or null
+    const int* n_obs;            // [B] or null
+    const int* done;             // [B] or null: finished egos keep their cut (and still act as obstacles)
+    int* agent_idx;              // [B] io  traj_agent_idx
+    int* ncourse;                // [B] io  in: previous cut length (0 = no tmp_trajectory yet), out: new cut length
+    int* collided;               // [B] out
+    int* coll_idx;               // [B] out  index into full[agent_idx:], -1 if none
+    double* coll_xy;             // [B,2] out (NaN if none)
+    int* n_res;                  // [B] out  length of the resampled ego prediction
+    int* flags;                  // [B] out  bit0: nearest-index inconsistency, bit1: resample overflow
+    double circ[2];              // circle centre offsets along the body axis (front, back)
+    double radius, wheelbase, dt, max_accel, max_speed;
+    int frame_window, n_frames;
+};
+
+namespace mpcb {
+
+struct CouplingSmem {
+    double cum[32];                                        // chunk of the sequential cumulative distance
+    int res_idx[MPCB_CP_MAX_RES];                          // path index of every kept ego frame
+    double ocx[MPCB_CP_MAX_OBS][2][MPCB_CP_FRAMES];        // obstacle circle centres per frame
+    double ocy[MPCB_CP_MAX_OBS][2][MPCB_CP_FRAMES];
+};
+
+// exact `sqrt(dx*dx + dy*dy) <= thr` with the square root taken only inside the rounding band
+__device__ __forceinline__ bool within(double ax, double ay, double bx, double by, double thr, double thr2) {
+    const double dx = __dsub_rn(ax, bx), dy = __dsub_rn(ay, by);
+    const double s = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+    if (s < thr2 * (1.0 - 1e-12)) return true;
+    if (s > thr2 * (1.0 + 1e-12)) return false;
+    return __dsqrt_rn(s) <= thr;
+}
+
+// forward declaration (mpcb_step.cuh)
+__device__ __forceinline__ int nearest_index_in_direction(const double* __restrict__ cx, const double* __restrict__ cy,
+                                                          int start, int nc, double x, double y, int lane);
+
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) coupling_kernel(const CouplingParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int b = blockIdx.x * WARPS + wid;
+    if (b >= p.B) return;
+    if (p.done && p.done[b] != 0) return;
+    CouplingSmem& sm = reinterpret_cast<CouplingSmem*>(smem_raw)[wid];
+    const double x0 = p.state[4 * b], y0 = p.state[4 * b + 1], v0 = p.state[4 * b + 3];
+    const int route = p.route[b];
+    const int ncf = p.course_len[route];
+    const double* __restrict__ cx = p.courses + (size_t)route * 3 * p.ncmax;
+    const double* __restrict__ cy = cx + p.ncmax;
+    const double* __restrict__ cyaw = cy + p.ncmax;
+    const double* __restrict__ pcc = p.pathcc + (size_t)route * 4 * p.ncmax;     // [circle][x|y][ncmax]
+    const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+
+    // ---- 1. traj_agent_idx (mpc_intersection.py:103-105) ------------------------------------------------------
+    int aidx = p.agent_idx[b];
+    const int ncp = p.ncourse[b];
+    bool upd = true;
+    if (ncp > 0) upd = (cx[aidx] != cx[ncp - 1]) || (cy[aidx] != cy[ncp - 1]) || (cyaw[aidx] != cyaw[ncp - 1]);
+    if (upd) {
+        const int ni = nearest_index_in_direction(cx, cy, aidx, ncf, x0, y0, lane);
+        if (ni < 0) { if (lane == 0 && p.flags) p.flags[b] = 1; return; }      // the reference raises (trajectories.py:120)
+        aidx = ni;
+    }
+    const int n = ncf - aidx;                                      // len(trajectory_full[traj_agent_idx:]) >= 1
+    int flags = 0;
+
+    // ---- 2. ego prediction: resample_curve with per-point spacing (mpc_intersection.py:110-116) ---------------
+    int nres = 0;
+    {
+        const bool ramp = v0 < p.max_speed;
+        const double dl_const = __dmul_rn(p.dt, p.max_speed);
+        double acc = 0.0, acc_a = 0.0;
+        long long q_carry = 0;
+        for (int base = 0; base < n; base += 32) {
+            const int i = base + lane;
+            const bool valid = i < n;
+            double dist = 0.0;
+            if (valid && i > 0) {
+                const double dx = __dsub_rn(cx[aidx + i], cx[aidx + i - 1]), dy = __dsub_rn(cy[aidx + i], cy[aidx + i - 1]);
+                dist = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+            }
+            __syncwarp();
+            sm.cum[lane] = dist;
+            __syncwarp();
+            double mycum = 0.0, mya = 0.0;
+#pragma unroll 8
+            for (int j = 0; j < 32; ++j) {                         // np.cumsum is sequential
+                acc = __dadd_rn(acc, sm.cum[j]);
+                acc_a = __dadd_rn(acc_a, p.max_accel);
+                if (j == lane) { mycum = acc; mya = acc_a; }
+            }
+            const double dl_i = ramp ? __dmul_rn(p.dt, fmin(__dadd_rn(mya, v0), p.max_speed)) : dl_const;
+            const long long q = valid ? (long long)floor(__ddiv_rn(mycum, dl_i)) : 0;
+            long long qprev = __shfl_up_sync(MPCB_FULL, q, 1);
+            if (lane == 0) qprev = q_carry;
+            q_carry = __shfl_sync(MPCB_FULL, q, 31);
+            const bool keep = valid && (i == 0 || (q - qprev) >= 1 || i == n - 1);
+            const unsigned bal = __ballot_sync(MPCB_FULL, keep);
+            const int pos = nres + __popc(bal & ((1u << lane) - 1u));
+            if (keep) { if (pos < MPCB_CP_MAX_RES) sm.res_idx[pos] = aidx + i; else flags |= 2; }
+            nres += __popc(bal);
+        }
+        flags = __reduce_or_sync(MPCB_FULL, flags);
+        if (nres > MPCB_CP_MAX_RES) nres = MPCB_CP_MAX_RES;
+    }
+
+    // ---- 3. obstacle predictions (moving_obstacles_prediction.py:21-47), lane o <-> obstacle o ----------------------
+    int n_o;
+    if (p.vehicles_per_scenario > 0) n_o = p.vehicles_per_scenario - 1;
+    else n_o = p.n_obs ? p.n_obs[b] : 0;
+    n_o = min(n_o, MPCB_CP_MAX_OBS);
+    if (lane < n_o) {
+        double ox, oy, ov, oyaw, oa, ost;
+        if (p.vehicles_per_scenario > 0) {          // the other egos of this scenario, constant speed, zero steer
+            const int V = p.vehicles_per_scenario, s0 = (b / V) * V, me = b - s0;
+            const int other = s0 + (lane < me ? lane : lane + 1);
+            ox = p.state[4 * other]; oy = p.state[4 * other + 1]; oyaw = p.state[4 * other + 2]; ov = p.state[4 * other + 3];
+            oa = 0.0; ost = 0.0;
+        } else {
+            const double* o6 = p.obs + ((size_t)b * MPCB_CP_MAX_OBS + lane) * 6;
+            ox = o6[0]; oy = o6[1]; ov = o6[2]; oyaw = o6[3]; oa = o6[4]; ost = o6[5];
+        }
+        const double tn = tan(ost);
+        for (int f = 0; f < p.n_frames; ++f) {
+            double sn, cs;
+            sincos(oyaw, &sn, &cs);
+            ox = __dadd_rn(ox, __dmul_rn(__dmul_rn(ov, cs), p.dt));
+            oy = __dadd_rn(oy, __dmul_rn(__dmul_rn(ov, sn), p.dt));
+            ov = __dadd_rn(ov, __dmul_rn(oa, p.dt));
+            oyaw = __dadd_rn(oyaw, __dmul_rn(__dmul_rn(__ddiv_rn(ov, p.wheelbase), tn), p.dt));
+            sincos(oyaw, &sn, &cs);
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {           // trajectories.py:28-34 with y_offset = 0
+                sm.ocx[lane][c][f] = __dadd_rn(__dmul_rn(cs, p.circ[c]), ox);
+                sm.ocy[lane][c][f] = __dadd_rn(__dmul_rn(sn, p.circ[c]), oy);
+            }
+        }
+    }
+    __syncwarp();
+
+    // ---- 4. first colliding pair in the reference's row order: frame, agent circle, obstacle, offset, obstacle circle
+    const double thr = 2.0 * p.radius, thr2 = thr * thr;
+    const int W = 2 * p.frame_window + 1, nf = p.n_frames;
+    bool hit = false;
+    double hx = 0.0, hy = 0.0;
+    if (n_o > 0) {
+        const int n_it = max(nres, nf);
+        for (int f = 0; f < n_it && !hit; ++f) {
+            const int pidx = sm.res_idx[min(f, nres - 1)];
+            const int g = min(f, nf - 1);
+            for (int a = 0; a < 2 && !hit; ++a) {
+                const double ax = pcc[(2 * a) * p.ncmax + pidx], ay = pcc[(2 * a + 1) * p.ncmax + pidx];
+                for (int o = 0; o < n_o && !hit; ++o) {
+                    for (int base = 0; base < 2 * W; base += 32) {
+                        const int idx = base + lane;
+                        bool h = false;
+                        double px = 0.0, py = 0.0;
+                        if (idx < 2 * W) {
+                            const int k = idx >> 1, c = idx & 1;
+                            const int src = min(max(g - (k - p.frame_window), 0), nf - 1);
+                            px = sm.ocx[o][c][src]; py = sm.ocy[o][c][src];
+                            h = within(ax, ay, px, py, thr, thr2);
+                        }
+                        const unsigned bal = __ballot_sync(MPCB_FULL, h);
+                        if (bal) {
+                            const int src_lane = __ffs(bal) - 1;
+                            hx = shfl(px, src_lane); hy = shfl(py, src_lane);
+                            hit = true;
+                            break;
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    // ---- 5. where on the un-resampled path, and the cut (collision_avoidance.py:83-119, mpc_intersection.py:129-136)
+    int cidx = -1, cutoff = ncf;
+    double cxy_x = qnan, cxy_y = qnan;
+    if (hit) {
+        cidx = 0;                                                  // np.argmax of an all-False mask
+        bool found = false;
+        for (int c = 0; c < 2 && !found; ++c)
+            for (int base = 0; base < n; base += 32) {
+                const int i = base + lane;
+                const bool h = i < n && within(hx, hy, pcc[(2 * c) * p.ncmax + aidx + i], pcc[(2 * c + 1) * p.ncmax + aidx + i], thr, thr2);
+                const unsigned bal = __ballot_sync(MPCB_FULL, h);
+                if (bal) { cidx = base + __ffs(bal) - 1; found = true; break; }
+            }
+        cxy_x = cx[aidx + cidx]; cxy_y = cy[aidx + cidx];
+        int j = -1;
+        for (int base = 0; base < ncf; base += 32) {
+            const int i = base + lane;
+            const bool h = i < ncf && within(cx[i], cy[i], cxy_x, cxy_y, 0.001, 0.001 * 0.001);
+            const unsigned bal = __ballot_sync(MPCB_FULL, h);
+            if (bal) { j = base + __ffs(bal) - 1; break; }
+        }
+        const int extra = 4 * (int)ceil(__ddiv_rn(p.radius, p.dl[route]));
+        cutoff = max(aidx + 1, j - extra);
+    }
+    if (lane == 0) {
+        p.agent_idx[b] = aidx;
+        p.ncourse[b] = cutoff;
+        if (p.collided) p.collided[b] = hit ? 1 : 0;
+        if (p.coll_idx) p.coll_idx[b] = cidx;
+        if (p.coll_xy) { p.coll_xy[2 * b] = cxy_x; p.coll_xy[2 * b + 1] = cxy_y; }
+        if (p.n_res) p.n_res[b] = nres;
+        if (p.flags) p.flags[b] = flags;
+    }
+}
+
+}  // namespace mpcb

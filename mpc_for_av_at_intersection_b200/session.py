@@ -30,6 +30,9 @@ _FIELDS = {
     "ncourse": (_lib.F_NCOURSE, np.int32, lambda T: ()),
     "route": (_lib.F_ROUTE, np.int32, lambda T: ()),
     "goal": (_lib.F_GOAL, np.float64, lambda T: (2,)),
+    "agent_idx": (_lib.F_AGENT_IDX, np.int32, lambda T: ()),
+    "collided": (_lib.F_COLLIDED, np.int32, lambda T: ()),
+    "coll_idx": (_lib.F_COLL_IDX, np.int32, lambda T: ()),
 }
 
 
@@ -101,6 +104,32 @@ class MpcSession:
             self._h, int(nsteps), C.c_void_p(history_ptr) if history_ptr else None, 0 if goal_test else 1,
             C.c_void_p(cuda_stream)),
             self._h, "mpcb_session_closed_loop_dev")
+
+    def multi_agent_dev(self, nsteps: int, vehicles_per_scenario: int, history_ptr: int = 0, cuda_stream: int = 0,
+                        goal_test: bool = True):
+        """nsteps x (is_goal | coupling against the other egos of the scenario | MPC.step | Simulation.step) on the
+        resident session: problems are grouped in scenarios of `vehicles_per_scenario` consecutive egos."""
+        _lib.check(self._lib.mpcb_session_multi_agent_dev(
+            self._h, int(nsteps), int(vehicles_per_scenario), C.c_void_p(history_ptr) if history_ptr else None,
+            0 if goal_test else 1, C.c_void_p(cuda_stream)), self._h, "mpcb_session_multi_agent_dev")
+
+    def coupling(self, state, route, agent_idx, ncourse, obs=None, n_obs=None, vehicles_per_scenario=0):
+        """Row A9 with host buffers (mpcb_coupling_host): the coupling part of the reference loop body
+        (main/scenarios/mpc_intersection.py:100-139) for B egos.  agent_idx / ncourse are updated in place.
+        obs [B, MAX_OBSTACLES, 6] rows (x, y, v, yaw, a, steer), n_obs [B]."""
+        B = len(state)
+        for a, dt in ((state, np.float64), (route, np.int32), (agent_idx, np.int32), (ncourse, np.int32)):
+            assert a.dtype == dt and a.flags.c_contiguous and len(a) == B
+        if obs is not None:
+            assert obs.dtype == np.float64 and obs.shape == (B, _lib.MAX_OBSTACLES, 6) and obs.flags.c_contiguous
+            assert n_obs is not None and n_obs.dtype == np.int32 and n_obs.shape == (B,)
+        out = dict(collided=np.zeros(B, np.int32), coll_idx=np.zeros(B, np.int32), coll_xy=np.zeros((B, 2)),
+                   n_res=np.zeros(B, np.int32), flags=np.zeros(B, np.int32))
+        _lib.check(self._lib.mpcb_coupling_host(
+            self._h, B, _p(state), _p(route), _p(obs), _p(n_obs), _p(agent_idx), _p(ncourse), _p(out["collided"]),
+            _p(out["coll_idx"]), _p(out["coll_xy"]), _p(out["n_res"]), _p(out["flags"]), int(vehicles_per_scenario)),
+            self._h, "mpcb_coupling_host")
+        return out
 
     # ---- attribute access -----------------------------------------------------------------------------------
     def _meta(self, name):

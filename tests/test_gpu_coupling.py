@@ -1,0 +1,112 @@
+"""Row A9 on the GPU (mpcb_coupling through the C ABI) against the vectors recorded from the reference's own
+functions and against the numpy oracle on fresh scenes.  Integer outputs and flags must be bit-exact."""
+import numpy as np
+import pytest
+
+import collision_oracle as co
+from conftest import golden, load_routes
+
+pytestmark = pytest.mark.gpu
+CARS = [(2.86, 2.0, 3.5), (4.0, 2.04, 4.84)]
+
+
+def _session(car=0, T=20):
+    from mpc_for_av_at_intersection_b200 import CourseSet, MpcConfig, MpcSession
+    L, w, ln = CARS[car]
+    cfg = MpcConfig.from_json(T=T, wheelbase=L, car_width=w, car_length=ln)
+    return MpcSession(cfg, CourseSet(load_routes(False)), 1024), cfg
+
+
+def _pack_obs(obs_list):
+    from mpc_for_av_at_intersection_b200 import _lib
+    B = len(obs_list)
+    obs = np.zeros((B, _lib.MAX_OBSTACLES, 6))
+    n = np.zeros(B, np.int32)
+    for b, o in enumerate(obs_list):
+        n[b] = len(o)
+        obs[b, :len(o)] = o
+    return obs, n
+
+
+@pytest.mark.parametrize("car", [0, 1])
+def test_random_scenes_match_reference(car, routes_smooth):
+    g = golden("collision_random.npz")
+    sel = np.flatnonzero(g["car"] == car)
+    ses, cfg = _session(car)
+    route = g["route"][sel].astype(np.int32)
+    state = np.zeros((len(sel), 4))
+    for i, k in enumerate(sel):      # the ego sits exactly on its path point: the nearest-index update keeps agent_idx
+        full = routes_smooth[int(g["route"][k])]
+        j = int(g["agent_idx"][k])
+        state[i] = (full[j, 0], full[j, 1], full[j, 2], g["v"][k])
+    agent_idx = g["agent_idx"][sel].astype(np.int32)
+    ncourse = np.zeros(len(sel), np.int32)
+    obs, n_obs = _pack_obs([g["obs"][k][:int(g["n_obs"][k])] for k in sel])
+    out = ses.coupling(state, route, agent_idx, ncourse, obs, n_obs)
+    assert (out["flags"] == 0).all()
+    # an ego placed on path point j of a path of n >= 3 remaining points resolves to j (or j + 1 for n == 2)
+    n_rem = np.array([len(routes_smooth[int(g["route"][k])]) for k in sel]) - g["agent_idx"][sel]
+    keep = n_rem != 2
+    assert np.array_equal(agent_idx[keep], g["agent_idx"][sel][keep])
+    assert np.array_equal(out["n_res"][keep], g["n_res"][sel][keep])
+    assert np.array_equal(out["collided"][keep], g["collided"][sel][keep])
+    assert np.array_equal(out["coll_idx"][keep], g["coll_idx"][sel][keep])
+    assert np.array_equal(ncourse[keep], g["cutoff_idx"][sel][keep])
+    hit = keep & (out["collided"] == 1)
+    assert np.array_equal(out["coll_xy"][hit, 0], g["coll_x"][sel][hit]) and np.array_equal(out["coll_xy"][hit, 1], g["coll_y"][sel][hit])
+    assert np.isnan(out["coll_xy"][keep & (out["collided"] == 0)]).all()
+    print(f"car {car}: {keep.sum()} scenes, {int(out['collided'][keep].sum())} collisions, all integer outputs identical")
+
+
+@pytest.mark.parametrize("T", [13, 20])
+def test_scripted_obstacle_loop_replay(T, routes_smooth):
+    """Every control step of the reference's obstacle scenario (mpc_intersection.py with two scripted cars)."""
+    g = golden(f"closed_loop_T{T}.npz")
+    sel = np.flatnonzero(g["loop"] == 12)
+    ses, cfg = _session(0, T)
+    B = len(sel)
+    state = np.ascontiguousarray(g["state"][sel])
+    route = g["route"][sel].astype(np.int32)
+    prev_idx = np.concatenate([[0], g["agent_idx"][sel][:-1]]).astype(np.int32)      # traj_agent_idx before the update
+    prev_nc = np.concatenate([[0], g["cutoff_idx"][sel][:-1]]).astype(np.int32)      # len(tmp_trajectory) of the previous step
+    obs, n_obs = _pack_obs([g["obs"][k] for k in sel])
+    agent_idx, ncourse = prev_idx.copy(), prev_nc.copy()
+    out = ses.coupling(state, route, agent_idx, ncourse, obs, n_obs)
+    assert (out["flags"] == 0).all()
+    assert np.array_equal(agent_idx, g["agent_idx"][sel])
+    assert np.array_equal(out["n_res"], g["n_res"][sel])
+    assert np.array_equal(out["collided"], g["collided"][sel])
+    assert np.array_equal(out["coll_idx"], g["coll_idx"][sel])
+    assert np.array_equal(ncourse, g["cutoff_idx"][sel])
+    assert np.array_equal(ncourse, g["ncourse"][sel])
+
+
+def test_against_oracle_on_fresh_scenes(routes_smooth):
+    rng = np.random.default_rng(11)
+    ses, cfg = _session(0)
+    B = 600
+    route = rng.integers(0, 12, B).astype(np.int32)
+    agent_idx = np.array([rng.integers(0, len(routes_smooth[r]) - 3) for r in route], np.int32)
+    state = np.zeros((B, 4))
+    obs_list = []
+    for b in range(B):
+        full = routes_smooth[route[b]]
+        j = agent_idx[b]
+        state[b] = (full[j, 0], full[j, 1], full[j, 2], rng.uniform(0, 8.3))
+        n = int(rng.integers(0, 8))
+        o = np.zeros((n, 6))
+        for i in range(n):
+            jj = min(len(full) - 1, j + int(rng.integers(0, 500)))
+            o[i] = (full[jj, 0] + rng.normal(0, 4), full[jj, 1] + rng.normal(0, 4), rng.uniform(0, 9), rng.uniform(-3, 3),
+                    rng.choice([0.0, rng.uniform(-1, 1)]), rng.choice([0.0, rng.uniform(-0.4, 0.4)]))
+        obs_list.append(o)
+    obs, n_obs = _pack_obs(obs_list)
+    want_idx = agent_idx.copy()
+    ncourse = np.zeros(B, np.int32)
+    out = ses.coupling(state, route, agent_idx, ncourse, obs, n_obs)
+    assert np.array_equal(agent_idx, want_idx)
+    offs, radius = co.circle_offsets(*CARS[0])
+    for b in range(B):
+        ref = co.coupling_step(routes_smooth[route[b]], int(want_idx[b]), float(state[b, 3]), obs_list[b], offs, radius, 2.86)
+        got = (out["n_res"][b], out["collided"][b], out["coll_idx"][b], ncourse[b])
+        assert got == (ref["n_res"], ref["collided"], ref["coll_idx"], ref["cutoff_idx"]), (b, got, ref)
