@@ -40,13 +40,13 @@ def test_random_scenes_match_reference(car, routes_smooth):
         j = int(g["agent_idx"][k])
         state[i] = (full[j, 0], full[j, 1], full[j, 2], g["v"][k])
     agent_idx = g["agent_idx"][sel].astype(np.int32)
-    ncourse = np.zeros(len(sel), np.int32)
+    # previous cut = agent_idx + 1: the path had collapsed onto the ego's point, so the reference skips the
+    # nearest-index update (mpc_intersection.py:103) and the recorded agent_idx is used as is
+    ncourse = (agent_idx + 1).astype(np.int32)
     obs, n_obs = _pack_obs([g["obs"][k][:int(g["n_obs"][k])] for k in sel])
     out = ses.coupling(state, route, agent_idx, ncourse, obs, n_obs)
     assert (out["flags"] == 0).all()
-    # an ego placed on path point j of a path of n >= 3 remaining points resolves to j (or j + 1 for n == 2)
-    n_rem = np.array([len(routes_smooth[int(g["route"][k])]) for k in sel]) - g["agent_idx"][sel]
-    keep = n_rem != 2
+    keep = np.ones(len(sel), bool)
     assert np.array_equal(agent_idx[keep], g["agent_idx"][sel][keep])
     assert np.array_equal(out["n_res"][keep], g["n_res"][sel][keep])
     assert np.array_equal(out["collided"][keep], g["collided"][sel][keep])
@@ -102,7 +102,7 @@ def test_against_oracle_on_fresh_scenes(routes_smooth):
         obs_list.append(o)
     obs, n_obs = _pack_obs(obs_list)
     want_idx = agent_idx.copy()
-    ncourse = np.zeros(B, np.int32)
+    ncourse = (agent_idx + 1).astype(np.int32)
     out = ses.coupling(state, route, agent_idx, ncourse, obs, n_obs)
     assert np.array_equal(agent_idx, want_idx)
     offs, radius = co.circle_offsets(*CARS[0])
