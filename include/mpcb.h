@@ -211,7 +211,7 @@ int mpcb_session_store_host(mpcb_handle* h, int what, const void* src, long long
  *                 ibid.:124-210).  0: obstacles come from obs_dev. */
 #define MPCB_MAX_OBSTACLES 8
 int mpcb_coupling(mpcb_handle* h, int B, const double* state_dev, const int* route_dev, const double* obs_dev,
-                  const int* n_obs_dev, const int* done_dev, int* agent_idx_dev, int* ncourse_dev, int* collided_dev,
+                  const int* n_obs_dev, int* done_dev, int* agent_idx_dev, int* ncourse_dev, int* collided_dev,
                   int* coll_idx_dev, double* coll_xy_dev, int* n_res_dev, int* flags_dev, int vehicles_per_scenario,
                   void* stream);
 /* same with HOST buffers (synchronous); in/out arrays are updated in place */

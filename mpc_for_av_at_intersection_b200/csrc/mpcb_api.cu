@@ -643,7 +643,7 @@ int launch_coupling(mpcb_handle* h, CouplingParams& p, cudaStream_t st) {
 extern "C" {
 
 int mpcb_coupling(mpcb_handle* h, int B, const double* state_dev, const int* route_dev, const double* obs_dev,
-                  const int* n_obs_dev, const int* done_dev, int* agent_idx_dev, int* ncourse_dev, int* collided_dev,
+                  const int* n_obs_dev, int* done_dev, int* agent_idx_dev, int* ncourse_dev, int* collided_dev,
                   int* coll_idx_dev, double* coll_xy_dev, int* n_res_dev, int* flags_dev, int vehicles_per_scenario,
                   void* stream) {
     if (!h) return MPCB_EINVAL;
@@ -700,13 +700,22 @@ int mpcb_session_multi_agent_dev(mpcb_handle* h, int nsteps, int vehicles_per_sc
     if (!h || h->ses.B <= 0 || nsteps <= 0 || vehicles_per_scenario < 1) { if (h) h->err = "mpcb_session_multi_agent_dev: bad arguments / no session"; return MPCB_EINVAL; }
     auto& s = h->ses;
     h->last_stream = (cudaStream_t)stream; h->last_stream_set = true;
+    if (vehicles_per_scenario > MPCB_CP_MAX_OBS + 1 || s.B % vehicles_per_scenario != 0) {
+        h->err = "mpcb_session_multi_agent_dev: vehicles_per_scenario must be 1..9 and divide B"; return MPCB_EINVAL;
+    }
     StepParams p = session_params(h);
-    p.done = s.done; p.goal = s.goal; p.state_out = s.state; p.fuse_goal = (flags & MPCB_CL_NO_GOAL_TEST) ? 0 : 1; p.fuse_plant = 1;
+    p.done = s.done; p.goal = s.goal; p.state_out = s.state; p.fuse_goal = 0; p.fuse_plant = 1;
     for (int k = 0; k < nsteps; ++k) {
-        // egos that already satisfy is_goal must not be re-planned: the step kernel sets done at its head, the
-        // coupling kernel of the NEXT step skips them; all egos read start-of-step states (Jacobi order)
-        int rc = mpcb_coupling(h, s.B, s.state, s.route, nullptr, nullptr, s.done, s.agent_idx, s.ncourse, s.collided,
-                               s.coll_idx, nullptr, nullptr, nullptr, vehicles_per_scenario, stream);
+        // loop head of the reference (mpc_intersection.py:97): is_goal against the path as cut by the previous step,
+        // evaluated inside the coupling kernel; then the cut; then mpc.step + simulation.step.  All egos read
+        // start-of-step states (Jacobi order); finished egos stay where they are and still act as obstacles.
+        CouplingParams cp;
+        memset(&cp, 0, sizeof(cp));
+        cp.B = s.B; cp.vehicles_per_scenario = vehicles_per_scenario; cp.state = s.state; cp.route = s.route;
+        cp.done = s.done; cp.agent_idx = s.agent_idx; cp.ncourse = s.ncourse; cp.collided = s.collided; cp.coll_idx = s.coll_idx;
+        cp.goal = s.goal; cp.target_ind = s.target; cp.fuse_goal = (flags & MPCB_CL_NO_GOAL_TEST) ? 0 : 1;
+        cp.goal_dis = h->cfg.goal_dis; cp.stop_speed = h->cfg.stop_speed;
+        int rc = launch_coupling(h, cp, (cudaStream_t)stream);
         if (rc != MPCB_OK) return rc;
         p.history = history_dev ? history_dev + (size_t)k * 8 * s.B : nullptr;
         rc = dispatch_step(h, p, (cudaStream_t)stream);

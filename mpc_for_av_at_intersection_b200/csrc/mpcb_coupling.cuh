@@ -26,7 +26,11 @@ struct CouplingParams {
     const int* route;            // [B]
     const double* obs;           // [B, MPCB_CP_MAX_OBS, 6] x y v yaw a steer (MovingObstacle*.get()), or null
     const int* n_obs;            // [B] or null
-    const int* done;             // [B] or null: finished egos keep their cut (and still act as obstacles)
+    int* done;                   // [B] or null: finished egos keep their cut (and still act as obstacles)
+    const double* goal;          // [B,2], target_ind [B]: with fuse_goal the loop-head test MPC.is_goal
+    const int* target_ind;       //   (mpc_intersection.py:97, mpc.py:310-326) runs here, against the PREVIOUS cut
+    int fuse_goal;
+    double goal_dis, stop_speed;
     int* agent_idx;              // [B] io  traj_agent_idx
     int* ncourse;                // [B] io  in: previous cut length (0 = no tmp_trajectory yet), out: new cut length
     int* collided;               // [B] out
@@ -72,6 +76,14 @@ __global__ void __launch_bounds__(WARPS * 32) coupling_kernel(const CouplingPara
     const double x0 = p.state[4 * b], y0 = p.state[4 * b + 1], v0 = p.state[4 * b + 3];
     const int route = p.route[b];
     const int ncf = p.course_len[route];
+    if (p.fuse_goal) {
+        const int nc_prev = p.ncourse[b] > 0 ? p.ncourse[b] : ncf;      // len(mpc.cx) before this step's cut
+        const double gd = hypot(x0 - p.goal[2 * b], y0 - p.goal[2 * b + 1]);
+        if (gd <= p.goal_dis && abs(p.target_ind[b] - nc_prev) < 5 && fabs(v0) <= p.stop_speed) {
+            if (lane == 0) p.done[b] = 1;
+            return;
+        }
+    }
     const double* __restrict__ cx = p.courses + (size_t)route * 3 * p.ncmax;
     const double* __restrict__ cy = cx + p.ncmax;
     const double* __restrict__ cyaw = cy + p.ncmax;

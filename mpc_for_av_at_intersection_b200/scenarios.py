@@ -54,3 +54,36 @@ def host_plant_step(state, delta, accel, L, dt, max_steer=np.deg2rad(45.0), max_
     out[:, 2] = yaw + ((v / L) * np.tan(d)) * dt
     out[:, 3] = np.clip(v + accel * dt, min_speed, max_speed)
     return out
+
+
+def make_multi_agent_workload(courses, n_scenarios, vehicles=8, seed=1236, first=0, lane_span=15.0, min_gap=6.0,
+                              v_max=5.0):
+    """BASELINE.json configs[2]: per scenario `vehicles` egos on routes drawn from the 12
+    (start lane, turn) pairs, at most 3 per start lane, placed on the approach lane at offsets in [0, lane_span]
+    with gaps >= min_gap, initial speed U[0, v_max].  Ego k of scenario s is problem s*vehicles + k.
+    Assumes route id = 3*lane + turn (the order of load_intersection_routes)."""
+    n = n_scenarios * vehicles
+    route = np.empty(n, np.int32)
+    state = np.empty((n, 4))
+    index0 = np.empty(n, np.int32)
+    lanes = courses.R // 3
+    assert vehicles <= 3 * lanes
+    slots = np.repeat(np.arange(lanes), 3)
+    for s in range(n_scenarios):
+        rng = np.random.Generator(np.random.Philox(key=[np.uint64(seed), np.uint64(first + s)]))
+        lane_of = rng.permutation(slots)[:vehicles]
+        turn = rng.integers(0, 3, vehicles)
+        off = np.zeros(vehicles)
+        for ln in range(lanes):
+            idx = np.flatnonzero(lane_of == ln)
+            k = len(idx)
+            if k:
+                base = np.sort(rng.uniform(0.0, lane_span - min_gap * (k - 1), k))
+                off[idx] = base + min_gap * np.arange(k)
+        r = (3 * lane_of + turn).astype(np.int32)
+        i0 = np.rint(off / courses.dl[r]).astype(np.int32)
+        sl = slice(s * vehicles, (s + 1) * vehicles)
+        route[sl], index0[sl] = r, i0
+        state[sl, 0], state[sl, 1], state[sl, 2] = courses.packed[r, 0, i0], courses.packed[r, 1, i0], courses.packed[r, 2, i0]
+        state[sl, 3] = rng.uniform(0.0, v_max, vehicles)
+    return dict(route=route, state=state, target_ind=np.maximum(index0 - 3, 0).astype(np.int32), index0=index0)

@@ -135,3 +135,60 @@ def coupling_step(full, agent_idx, v, obstacles, offs, radius, L, dt=0.2, max_ac
         out.update(collided=1, coll_x=hit["x"], coll_y=hit["y"], coll_idx=hit["idx"], row=hit["row"],
                    cutoff_idx=max(agent_idx + 1, j - extra_margin))
     return out
+
+
+def agent_index_update(full, agent_idx, ncourse_prev, x, y):
+    """main/scenarios/mpc_intersection.py:103-105: skip the update when the cut path has collapsed onto the
+    ego's point (ncourse_prev = len(tmp_trajectory) of the previous step, 0 = None).  -1 = the reference raises."""
+    import mpc_oracle as mo
+    if ncourse_prev > 0 and not np.any(full[agent_idx, :3] != full[ncourse_prev - 1, :3]):
+        return agent_idx
+    return mo.nearest_index_in_direction(x, y, full[:, 0], full[:, 1], agent_idx)
+
+
+def multi_agent_closed_loop(routes_smooth, route, state0, target0, nsteps, T, offs, radius, L, dt=0.2):
+    """SURVEY.md section 8a, A9 spec for config 3: every ego takes the OTHER egos of its scenario as obstacles
+    (constant speed, zero steer), Jacobi order.  `route/state0/target0` describe ONE scenario of V vehicles.
+    Returns history [nsteps, V, 8] (NaN rows once an ego is done), done[V], ncourse log [nsteps, V]."""
+    import mpc_oracle as mo
+    V = len(route)
+    cfg = mo.Cfg.from_dict({"T": T})
+    mpcs = []
+    for j in range(V):
+        full = routes_smooth[route[j]]
+        m = mo.OracleMPC(full[:, 0].copy(), full[:, 1].copy(), full[:, 2].copy(),
+                         float(np.linalg.norm(full[0, :2] - full[1, :2])), L, dt, cfg)
+        m.target_ind = int(target0[j])
+        mpcs.append(m)
+    state = np.array(state0, float)
+    agent_idx = np.zeros(V, int)
+    ncourse = np.zeros(V, int)
+    done = np.zeros(V, int)
+    hist = np.full((nsteps, V, 8), np.nan)
+    nclog = np.zeros((nsteps, V), int)
+    for k in range(nsteps):
+        new_state = state.copy()
+        for j in range(V):
+            if done[j]:
+                nclog[k, j] = ncourse[j]
+                continue
+            full = routes_smooth[route[j]]
+            m = mpcs[j]
+            if m.is_goal(state[j]):                 # loop head, with the path as cut by the PREVIOUS step (:97)
+                done[j] = 1
+                nclog[k, j] = ncourse[j]
+                continue
+            ai = agent_index_update(full, int(agent_idx[j]), int(ncourse[j]), state[j, 0], state[j, 1])
+            assert ai >= 0
+            agent_idx[j] = ai
+            others = [(state[i, 0], state[i, 1], state[i, 3], state[i, 2], 0.0, 0.0) for i in range(V) if i != j]
+            c = coupling_step(full, ai, state[j, 3], others, offs, radius, L, dt)
+            ncourse[j] = c["cutoff_idx"]
+            nclog[k, j] = ncourse[j]
+            m.set_trajectory_fromarray(full[:ncourse[j]])
+            di, ai_ = m.step(state[j])
+            dev = m.get_current_xref_deviation() if (m.ox is not None and m.target_ind < len(m.cx)) else np.nan
+            new_state[j] = mo.plant_step(state[j, 0], state[j, 1], state[j, 2], state[j, 3], ai_, di, L, dt)
+            hist[k, j] = (*new_state[j], di, ai_, dev, m.status)
+        state = new_state
+    return hist, done, nclog

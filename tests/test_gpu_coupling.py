@@ -110,3 +110,37 @@ def test_against_oracle_on_fresh_scenes(routes_smooth):
         ref = co.coupling_step(routes_smooth[route[b]], int(want_idx[b]), float(state[b, 3]), obs_list[b], offs, radius, 2.86)
         got = (out["n_res"][b], out["collided"][b], out["coll_idx"][b], ncourse[b])
         assert got == (ref["n_res"], ref["collided"], ref["coll_idx"], ref["cutoff_idx"]), (b, got, ref)
+
+
+def test_multi_agent_closed_loop_matches_oracle(routes_smooth):
+    """BASELINE configs[2] spec: 8 interacting vehicles per scenario, every ego cut by the predicted
+    motion of the others, Jacobi order.  Device loop (2 launches per control step) vs the CPU composition of the
+    reference functions (oracle/collision_oracle.multi_agent_closed_loop): cut lengths and done flags bit-exact
+    every step, states within 1e-6 (the first 30 steps are before any sensitive turn segment)."""
+    from mpc_for_av_at_intersection_b200.scenarios import make_multi_agent_workload
+    ses, cfg = _session(0, 20)
+    V, S, K = 8, 2, 30
+    wl = make_multi_agent_workload(ses.courses, S, V, seed=21)
+    ses.begin(wl["route"], target_ind=wl["target_ind"])
+    ses.store("state", wl["state"])
+    offs, radius = co.circle_offsets(*CARS[0])
+    refs = [co.multi_agent_closed_loop(routes_smooth, wl["route"][s * V:(s + 1) * V], wl["state"][s * V:(s + 1) * V],
+                                       wl["target_ind"][s * V:(s + 1) * V], K, 20, offs, radius, 2.86) for s in range(S)]
+    cuts = 0
+    worst = 0.0
+    state_ref = wl["state"].copy()
+    for k in range(K):
+        ses.multi_agent_dev(1, V)
+        nc, st, done = ses.fetch("ncourse"), ses.fetch("state"), ses.fetch("done")
+        for s in range(S):
+            hist, done_ref, nclog = refs[s]
+            sl = slice(s * V, (s + 1) * V)
+            ran = ~np.isnan(hist[k, :, 0])
+            state_ref[sl][ran] = hist[k, ran, :4]
+            want_nc = np.where(nclog[k] > 0, nclog[k], ses.courses.length[wl["route"][sl]])
+            assert np.array_equal(nc[sl], want_nc), (k, s, nc[sl], want_nc)
+            cuts += int((nc[sl] < ses.courses.length[wl["route"][sl]]).sum())
+            worst = max(worst, np.abs(st[sl] - state_ref[sl]).max())
+    assert cuts > 20, "the scenarios must actually interact"
+    print(f"multi-agent: {S}x{V} vehicles, {K} steps, {cuts} path cuts, max|dstate|={worst:.2e}")
+    assert worst < 1e-6
