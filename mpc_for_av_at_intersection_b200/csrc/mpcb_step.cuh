@@ -39,10 +39,12 @@ struct WarpSmem {
     double HA[TRI];                            // cost Hessian, accel block (lower)
     double HC[TRI];                            // steer block (lower)
     double HB[T * T];                          // cross block d/a, [col j][row lane]
-    double L[LTRI];                            // unscaled factor columns: (r,k), r >= k, at offL(k) + r - k
+    alignas(16) double L[LTRI + 16];           // unscaled factor columns (+ slack for the lanes >= T): (r,k), r >= k, at offL(k) + r - k
     double inv[N];                             // 1 / d_k
     double z[N];                               // broadcast slot of the fused forward solve
     double bc[8][T + 1];                       // per-stage broadcast tables used while assembling H
+    double tab[20][T];                         // per-stage model/weight coefficients, re-read by the gradient scans
+                                               // (keeps ~40 registers free for the matrix rows during the solve)
     __host__ __device__ static constexpr int offT(int j) { return j * T - j * (j - 1) / 2; }
     __host__ __device__ static constexpr int offL(int k) { return k * N - k * (k - 1) / 2; }
     // lanes read/write column k at row r; consecutive lanes -> consecutive addresses (conflict free); a lane
@@ -280,9 +282,17 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
             __syncwarp();
         }
 
+        if (act) {
+            const double tv[20] = {c_, s_, pp, qq, bb, pb, cn, snn, ppn, qqn, m11, m12, m22, wv, wp, rx, ry, rpsi, ra_w, rd_w};
+#pragma unroll
+            for (int i = 0; i < 20; ++i) sm.tab[i][lane] = tv[i];
+        }
+        __syncwarp();
+        auto tld = [&](int i) { return act ? sm.tab[i][lane] : 0.0; };
         // ---- linear prediction and objective gradient by scans ------------------------------------------
         // returns the states at index lane+1 (lanes < T); see oracle/condensed_model.py states()/grad()
         auto predict = [&](double a, double d, double& xs, double& ys, double& vs, double& phs) {
+            const double c_ = tld(0), s_ = tld(1), pp = tld(2), qq = tld(3), bb = tld(4), pb = tld(5);
             const double sa = scan_up(a, lane);
             const double bd_ = bb * d;
             const double sp_ = scan_up(bd_, lane);
@@ -296,6 +306,9 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
         auto gradient = [&](double a, double d, double& ga, double& gd) {
             double xs, ys, vs, phs;
             predict(a, d, xs, ys, vs, phs);
+            const double bb = tld(4), cn = tld(6), snn = tld(7), ppn = tld(8), qqn = tld(9), m11 = tld(10), m12 = tld(11),
+                         m22 = tld(12), wv = tld(13), wp = tld(14), rx = tld(15), ry = tld(16), rpsi = tld(17),
+                         ra_w = tld(18), rd_w = tld(19);
             const double ex = xs - rx, ey = ys - ry;
             const double lx = 2.0 * (m11 * ex + m12 * ey), ly = 2.0 * (m12 * ex + m22 * ey);
             const double lv = 2.0 * wv * vs, lp = 2.0 * wp * (phs - rpsi);      // xref[2,:] = 0 (mpc.py:102-105)
@@ -368,17 +381,18 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
             double sinv[8], w[8];
 #pragma unroll
             for (int c = 0; c < 8; ++c) { sinv[c] = rcp(s[c]); w[c] = lam[c] * sinv[c]; }
-            double A[T], Bm[T], C[T];
+            double A[T], Bm[T];
+            double dC, wr_prev;
             {
                 const double wv_suf = dt * dt * scan_dn(w[6] + w[7], lane);   // dt^2 * sum_{t>=lane}
                 const double wr = w[4] + w[5];
-                const double wr_prev = shfl_up1(wr, lane);
-                const double dA = w[0] + w[1], dC = w[2] + w[3] + wr + wr_prev;
+                wr_prev = shfl_up1(wr, lane);
+                const double dA = w[0] + w[1];
+                dC = w[2] + w[3] + wr + wr_prev;
 #pragma unroll
                 for (int j = 0; j < T; ++j) {
                     A[j] = (act ? sm.HA[WarpSmem<T>::offT(j) + lane - j] : 0.0) + wv_suf + (j == lane ? dA : 0.0);
                     Bm[j] = act ? sm.HB[j * T + lane] : 0.0;
-                    C[j] = (act ? sm.HC[WarpSmem<T>::offT(j) + lane - j] : 0.0) + (j == lane ? dC : 0.0) - (j == lane - 1 ? wr_prev : 0.0);
                 }
             }
             // affine right-hand side: -r_d + G'(lam - W r_p)
@@ -391,49 +405,87 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                 ra = ya - rda; rdl = yd - rdd;
             }
             // ---- LDL' factorisation, forward solve fused ---------------------------------------------------
+            // Column k is published to shared memory (it is the stored factor AND the broadcast operand of the
+            // rank-1 update); every lane then reads the pivot and forms 1/d_k itself, so no lane-divergent code.
+            // Stores of the cross-block rows by lanes >= T land in the not-yet-written head of column k+1.
+            using SM = WarpSmem<T>;
             bool bad = false;
+            double inva = 0.0, invd = 0.0;
 #pragma unroll
             for (int k = 0; k < T; ++k) {
-                if (act && lane >= k) sm.Lat(k, lane) = A[k];
-                if (act) sm.Lat(k, T + lane) = Bm[k];
-                if (lane == k) {
-                    bad = bad || !(A[k] > 0.0);
-                    sm.inv[k] = rcp(A[k]);
-                    sm.z[k] = ra;
-                }
+                if (lane >= k && act) sm.L[SM::offL(k) + lane - k] = A[k];
+                sm.L[SM::offL(k) + T + lane - k] = Bm[k];
+                if (lane == k) sm.z[k] = ra;
                 __syncwarp();
-                const double iv = sm.inv[k];
+                const double piv = sm.L[SM::offL(k)];
+                bad = bad || !(piv > 0.0);
+                const double iv = rcp(piv);
+                if (lane == k) { inva = iv; sm.inv[k] = iv; }
                 const double zk = sm.z[k] * iv;
                 const double la = A[k] * iv, lb = Bm[k] * iv;
                 if (lane > k) ra -= A[k] * zk;
                 rdl -= Bm[k] * zk;
+                {
+                    constexpr int dummy = 0; (void)dummy;
+                    int j = k + 1;
+                    if (((SM::offL(k) + j - k) & 1) && j < T) {
+                        const double cj = sm.L[SM::offL(k) + j - k];
+                        A[j] -= la * cj; Bm[j] -= lb * cj; ++j;
+                    }
 #pragma unroll
-                for (int j = k + 1; j < T; ++j) {
-                    const double cj = sm.Lat(k, j);
-                    A[j] -= la * cj;
-                    Bm[j] -= lb * cj;
+                    for (; j + 1 < T; j += 2) {
+                        const double2 cj = *reinterpret_cast<const double2*>(&sm.L[SM::offL(k) + j - k]);
+                        A[j] -= la * cj.x; Bm[j] -= lb * cj.x;
+                        A[j + 1] -= la * cj.y; Bm[j + 1] -= lb * cj.y;
+                    }
+                    if (j < T) {
+                        const double cj = sm.L[SM::offL(k) + j - k];
+                        A[j] -= la * cj; Bm[j] -= lb * cj;
+                    }
                 }
+            }
+            // steer block: assembled only now (the accel-block rows are dead), then the rank-T update
+            // C -= L21 D^-1 L21' with the cross-block factor rows still in registers
+            double C[T];
 #pragma unroll
-                for (int j = 0; j < T; ++j) C[j] -= lb * sm.Lat(k, T + j);
+            for (int j = 0; j < T; ++j)
+                C[j] = (act ? sm.HC[SM::offT(j) + lane - j] : 0.0) + (j == lane ? dC : 0.0) - (j == lane - 1 ? wr_prev : 0.0);
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < T; ++k) {
+                const double lb = Bm[k] * sm.inv[k];
+                int j = 0;
+                if ((SM::offL(k) + T - k) & 1) { C[0] -= lb * sm.L[SM::offL(k) + T - k]; j = 1; }
+#pragma unroll
+                for (; j + 1 < T; j += 2) {
+                    const double2 cj = *reinterpret_cast<const double2*>(&sm.L[SM::offL(k) + T + j - k]);
+                    C[j] -= lb * cj.x; C[j + 1] -= lb * cj.y;
+                }
+                if (j < T) C[j] -= lb * sm.L[SM::offL(k) + T + j - k];
             }
 #pragma unroll
             for (int k = 0; k < T; ++k) {
-                if (act && lane >= k) sm.Lat(T + k, T + lane) = C[k];
-                if (lane == k) {
-                    bad = bad || !(C[k] > 0.0);
-                    sm.inv[T + k] = rcp(C[k]);
-                    sm.z[T + k] = rdl;
-                }
+                if (lane >= k && act) sm.L[SM::offL(T + k) + lane - k] = C[k];
+                if (lane == k) sm.z[T + k] = rdl;
                 __syncwarp();
-                const double iv = sm.inv[T + k];
+                const double piv = sm.L[SM::offL(T + k)];
+                bad = bad || !(piv > 0.0);
+                const double iv = rcp(piv);
+                if (lane == k) { invd = iv; sm.inv[T + k] = iv; }
                 const double zk = sm.z[T + k] * iv;
                 const double lc = C[k] * iv;
                 if (lane > k) rdl -= C[k] * zk;
+                int j = k + 1;
+                if (((SM::offL(T + k) + j - k) & 1) && j < T) { C[j] -= lc * sm.L[SM::offL(T + k) + j - k]; ++j; }
 #pragma unroll
-                for (int j = k + 1; j < T; ++j) C[j] -= lc * sm.Lat(T + k, T + j);
+                for (; j + 1 < T; j += 2) {
+                    const double2 cj = *reinterpret_cast<const double2*>(&sm.L[SM::offL(T + k) + j - k]);
+                    C[j] -= lc * cj.x; C[j + 1] -= lc * cj.y;
+                }
+                if (j < T) C[j] -= lc * sm.L[SM::offL(T + k) + j - k];
             }
-            if (__any_sync(MPCB_FULL, bad)) { broke = true; break; }
-            const double inva = act ? sm.inv[lane] : 0.0, invd = act ? sm.inv[T + lane] : 0.0;
+            __syncwarp();
+            if (bad) { broke = true; break; }
 
             // back substitution  L' x = D^-1 z  (column-major factor, AXPY form)
             auto back_solve = [&](double za, double zd, double& xa, double& xd) {
