@@ -412,8 +412,12 @@ int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
 #ifdef MPCB_TUNE_VARIANTS
             switch (h->variant) {
                 case 1: return launch_step<20, 4, 3>(h, p, st);
-                case 2: return launch_step<20, 3, 5>(h, p, st);
-                case 3: return launch_step<20, 4, 4>(h, p, st);
+                case 2: return launch_step<20, 1, 8>(h, p, st);
+                case 3: return launch_step<20, 2, 4>(h, p, st);
+                case 4: return launch_step<20, 1, 12>(h, p, st);
+                case 5: return launch_step<20, 1, 10>(h, p, st);
+                case 6: return launch_step<20, 1, 9>(h, p, st);
+                case 7: return launch_step<20, 1, 14>(h, p, st);
                 default: break;
             }
 #endif

@@ -35,22 +35,102 @@ template <int T>
 struct WarpSmem {
     static constexpr int N = 2 * T;
     static constexpr int TRI = T * (T + 1) / 2;    // packed lower triangle, column major: (i,j), i >= j, at offT(j) + i - j
-    static constexpr int LTRI = N * (N + 1) / 2;
+    // factor storage.  Accel / steer blocks: packed lower, every column padded to an even length so that the entry
+    // (row k+j, column k) sits at parity j for every k (aligned 16-byte broadcast loads in a k-rolled loop).
+    // Cross block: full, column stride TSB (even; chosen so that row-wise reads by the back substitution are at
+    // most 2-way bank conflicted).
+    static constexpr int TE = (T + 1) & ~1;
+    static constexpr int TSB = TE + ((TE % 8 == 4) ? 2 : 0);
+    __host__ __device__ static constexpr int offT(int j) { return j * T - j * (j - 1) / 2; }
+    __host__ __device__ static constexpr int offP(int k) { return k * T - k * (k - 1) / 2 + ((T & 1) ? (k + 1) / 2 : k / 2); }
+    static constexpr int PTRI = offP(T);
     double HA[TRI];                            // cost Hessian, accel block (lower)
     double HC[TRI];                            // steer block (lower)
     double HB[T * T];                          // cross block d/a, [col j][row lane]
-    alignas(16) double L[LTRI + 16];           // unscaled factor columns (+ slack for the lanes >= T): (r,k), r >= k, at offL(k) + r - k
+    alignas(16) double LA[PTRI + 32];          // unscaled factor columns of the accel block
+    alignas(16) double LB[T * TSB + 32];       // cross block: column k (accel pivot k), rows = steer stages
+    alignas(16) double LC[PTRI + 32];          // Schur complement (steer block)
     double inv[N];                             // 1 / d_k
     double z[N];                               // broadcast slot of the fused forward solve
     double bc[8][T + 1];                       // per-stage broadcast tables used while assembling H
-    double tab[20][T];                         // per-stage model/weight coefficients, re-read by the gradient scans
-                                               // (keeps ~40 registers free for the matrix rows during the solve)
-    __host__ __device__ static constexpr int offT(int j) { return j * T - j * (j - 1) / 2; }
-    __host__ __device__ static constexpr int offL(int k) { return k * N - k * (k - 1) / 2; }
-    // lanes read/write column k at row r; consecutive lanes -> consecutive addresses (conflict free); a lane
-    // above the diagonal lands on the tail of the previous column (valid memory, value never used)
-    __device__ __forceinline__ double& Lat(int k, int r) { return L[offL(k) + r - k]; }
+    double tab[6][T];                          // per-stage model coefficients, re-read by the final prediction
 };
+
+// ---- k-rolled LDL' building blocks ---------------------------------------------------------------------------
+// The instruction cache, not the FP64 pipe, was the first limiter of the fully unrolled factorisation (ncu:
+// sm__icc_request_hit_rate 69 %, no_instruction the top stall): a warp keeps its matrix rows in a register window
+// that is SHIFTED by the rank-1 update itself (R[j-1] = R[j] - l * c[j]: the FMA writes one slot down), so the
+// pivot column is always slot 0 and the loop over pivots k is an ordinary loop.  JMAX = trailing columns kept.
+template <int T, int JMAX>
+__device__ __forceinline__ void ldl_accel_steps(WarpSmem<T>& sm, double (&R)[T], double (&Q)[T], int k0, int k1, int lane,
+                                                bool act, double wv_suf, double dA, double& ra, double& rdl, bool& bad,
+                                                double& inva, int& off) {
+    using SM = WarpSmem<T>;
+#pragma unroll 1
+    for (int k = k0; k < k1; ++k) {
+        const bool mine = lane == k;
+        const double a0 = R[0] + wv_suf + (mine ? dA : 0.0);          // G'WG terms join when the column is published
+        const double b0 = Q[0];
+        // lanes >= T store into the not-yet-written columns behind this one (rewritten after the barrier)
+        if (lane >= k) sm.LA[off + lane - k] = a0;
+        sm.LB[k * SM::TSB + lane] = b0;
+        if (mine) sm.z[k] = ra;
+        __syncwarp();
+        const double piv = sm.LA[off];
+        bad = bad || !(piv > 0.0);
+        const double iv = rcp(piv);
+        inva = mine ? iv : inva;
+        if (mine) sm.inv[k] = iv;
+        const double zk = sm.z[k] * iv;
+        const double la = a0 * iv, lb = b0 * iv;
+        if (lane > k) ra -= a0 * zk;
+        rdl -= b0 * zk;
+        if (JMAX >= 1) {
+            const double c1 = sm.LA[off + 1];
+            R[0] = R[1] - la * c1; Q[0] = Q[1] - lb * c1;
+        }
+#pragma unroll
+        for (int j = 2; j + 1 <= JMAX; j += 2) {
+            const double2 c = *reinterpret_cast<const double2*>(&sm.LA[off + j]);
+            R[j - 1] = R[j] - la * c.x; Q[j - 1] = Q[j] - lb * c.x;
+            R[j] = R[j + 1] - la * c.y; Q[j] = Q[j + 1] - lb * c.y;
+        }
+        if (JMAX >= 2 && (JMAX % 2) == 0) {
+            const double c = sm.LA[off + JMAX];
+            R[JMAX - 1] = R[JMAX] - la * c; Q[JMAX - 1] = Q[JMAX] - lb * c;
+        }
+        off += (T - k + 1) & ~1;
+    }
+}
+
+template <int T, int JMAX>
+__device__ __forceinline__ void ldl_steer_steps(WarpSmem<T>& sm, double (&C)[T], int k0, int k1, int lane, bool act,
+                                                double dC, double wr_prev, double& rdl, bool& bad, double& invd, int& off) {
+#pragma unroll 1
+    for (int k = k0; k < k1; ++k) {
+        const bool mine = lane == k;
+        const double c0 = C[0] + (mine ? dC : 0.0) - (lane == k + 1 ? wr_prev : 0.0);
+        if (lane >= k) sm.LC[off + lane - k] = c0;
+        if (mine) sm.z[T + k] = rdl;
+        __syncwarp();
+        const double piv = sm.LC[off];
+        bad = bad || !(piv > 0.0);
+        const double iv = rcp(piv);
+        invd = mine ? iv : invd;
+        const double zk = sm.z[T + k] * iv;
+        const double lc = c0 * iv;
+        if (lane > k) rdl -= c0 * zk;
+        if (JMAX >= 1) C[0] = C[1] - lc * sm.LC[off + 1];
+#pragma unroll
+        for (int j = 2; j + 1 <= JMAX; j += 2) {
+            const double2 c = *reinterpret_cast<const double2*>(&sm.LC[off + j]);
+            C[j - 1] = C[j] - lc * c.x;
+            C[j] = C[j + 1] - lc * c.y;
+        }
+        if (JMAX >= 2 && (JMAX % 2) == 0) C[JMAX - 1] = C[JMAX] - lc * sm.LC[off + JMAX];
+        off += (T - k + 1) & ~1;
+    }
+}
 
 // top-3 insertion keeping (d, idx) ascending; ties keep the earlier (lower) index first
 __device__ __forceinline__ void top3_insert(double d, int i, double (&bd)[3], int (&bi)[3]) {
@@ -169,7 +249,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
         if (!have_ov) {
             const double pstep = __dmul_rn(fabs(fmax(v0, p.min_ref_speed)), dt);    // |ov| * dt, mpc.py:96-98
             double acc = 0.0;
-#pragma unroll
+#pragma unroll 1
             for (int i = 0; i <= T; ++i) {
                 acc = (i == 0) ? pstep : __dadd_rn(acc, pstep);                     // np.cumsum is sequential
                 if (i == lane) trav = acc;
@@ -177,7 +257,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
         } else {
             const double term = __dmul_rn(fabs(sv), dt);
             double acc = 0.0;
-#pragma unroll
+#pragma unroll 1
             for (int i = 0; i <= T; ++i) {
                 const double ti = shfl(term, i);
                 acc = (i == 0) ? ti : __dadd_rn(acc, ti);
@@ -195,7 +275,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
         const double dcl = clampd(od, -p.max_steer, p.max_steer);
         const double tnd = act ? tan(dcl) : 0.0;
         double vb = v0, vcur = v0;
-#pragma unroll
+#pragma unroll 1
         for (int t = 0; t < T - 1; ++t) {
             const double at = shfl(oa, t);
             vcur = clampd(__dadd_rn(vcur, __dmul_rn(at, dt)), p.min_speed, p.max_speed);
@@ -203,7 +283,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
         }
         const double yterm = __dmul_rn(__dmul_rn(__ddiv_rn(vb, L), tnd), dt);
         double pb = yaw0, pcur = yaw0;
-#pragma unroll
+#pragma unroll 1
         for (int t = 0; t < T - 1; ++t) {
             pcur = __dadd_rn(pcur, shfl(yterm, t));
             if (lane == t + 1) pb = pcur;
@@ -264,7 +344,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
             __syncwarp();
             const double kA = 2.0 * dt * dt, kB = 2.0 * bb * dt, kC = 2.0 * bb;
             const int nb = (lane > 0 ? 1 : 0) + (lane < T - 1 ? 1 : 0);
-#pragma unroll
+#pragma unroll 1
             for (int j = 0; j < T; ++j) {
                 const double zxj = sm.bc[0][j], zyj = sm.bc[1][j], wxj = sm.bc[2][j], wyj = sm.bc[3][j];
                 double Aij = kA * (hA + zxj * gAx + zyj * gAy);
@@ -283,9 +363,9 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
         }
 
         if (act) {
-            const double tv[20] = {c_, s_, pp, qq, bb, pb, cn, snn, ppn, qqn, m11, m12, m22, wv, wp, rx, ry, rpsi, ra_w, rd_w};
+            const double tv[6] = {c_, s_, pp, qq, bb, pb};
 #pragma unroll
-            for (int i = 0; i < 20; ++i) sm.tab[i][lane] = tv[i];
+            for (int i = 0; i < 6; ++i) sm.tab[i][lane] = tv[i];
         }
         __syncwarp();
         auto tld = [&](int i) { return act ? sm.tab[i][lane] : 0.0; };
@@ -303,12 +383,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
             xs = x0 + scan_up(c_ * vt - pp * dph, lane);
             ys = y0 + scan_up(s_ * vt + qq * dph, lane);
         };
-        auto gradient = [&](double a, double d, double& ga, double& gd) {
+        // gradient of the cost by the forward/adjoint scans: used ONCE, at u = 0 (g0); inside the interior-point
+        // loop the gradient is g0 + H u from the stored Hessian (a 12-instruction rolled loop instead of 10 scans)
+        auto gradient_scan = [&](double a, double d, double& ga, double& gd) {
             double xs, ys, vs, phs;
             predict(a, d, xs, ys, vs, phs);
-            const double bb = tld(4), cn = tld(6), snn = tld(7), ppn = tld(8), qqn = tld(9), m11 = tld(10), m12 = tld(11),
-                         m22 = tld(12), wv = tld(13), wp = tld(14), rx = tld(15), ry = tld(16), rpsi = tld(17),
-                         ra_w = tld(18), rd_w = tld(19);
             const double ex = xs - rx, ey = ys - ry;
             const double lx = 2.0 * (m11 * ex + m12 * ey), ly = 2.0 * (m12 * ex + m22 * ey);
             const double lv = 2.0 * wv * vs, lp = 2.0 * wp * (phs - rpsi);      // xref[2,:] = 0 (mpc.py:102-105)
@@ -346,12 +425,22 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                 lam[c] = mk[c] ? 1.0 : 0.0;
             }
         }
-        double gscale;
-        {
-            double g0a, g0d;
-            gradient(0.0, 0.0, g0a, g0d);
-            gscale = 1.0 + warp_max(fmax(fabs(g0a), fabs(g0d)));
-        }
+        double gscale, g0a, g0d;
+        gradient_scan(0.0, 0.0, g0a, g0d);
+        gscale = 1.0 + warp_max(fmax(fabs(g0a), fabs(g0d)));
+        const int offt_lane = WarpSmem<T>::offT(act ? lane : 0);
+        auto gradient = [&](double a, double d, double& ga, double& gd) {
+            double sa = g0a, sd = g0d;
+#pragma unroll 2
+            for (int j = 0; j < T; ++j) {
+                const double aj = shfl(a, j), dj = shfl(d, j);
+                const int idx = (j <= lane) ? WarpSmem<T>::offT(j) + lane - j : offt_lane + j - lane;   // symmetric blocks
+                const int row = act ? lane : 0;
+                sa += sm.HA[idx] * aj + sm.HB[row * T + j] * dj;
+                sd += sm.HB[j * T + row] * aj + sm.HC[idx] * dj;
+            }
+            ga = act ? sa : 0.0; gd = act ? sd : 0.0;
+        };
         double res_d = 1e300, res_p = 1e300, mu = 1e300;
         bool converged = false, broke = false;
         int it = 0;
@@ -381,19 +470,14 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
             double sinv[8], w[8];
 #pragma unroll
             for (int c = 0; c < 8; ++c) { sinv[c] = rcp(s[c]); w[c] = lam[c] * sinv[c]; }
-            double A[T], Bm[T];
-            double dC, wr_prev;
+            using SM = WarpSmem<T>;
+            double dC, wr_prev, wv_suf, dA;
             {
-                const double wv_suf = dt * dt * scan_dn(w[6] + w[7], lane);   // dt^2 * sum_{t>=lane}
+                wv_suf = dt * dt * scan_dn(w[6] + w[7], lane);                // dt^2 * sum_{t>=lane}
                 const double wr = w[4] + w[5];
                 wr_prev = shfl_up1(wr, lane);
-                const double dA = w[0] + w[1];
+                dA = w[0] + w[1];
                 dC = w[2] + w[3] + wr + wr_prev;
-#pragma unroll
-                for (int j = 0; j < T; ++j) {
-                    A[j] = (act ? sm.HA[WarpSmem<T>::offT(j) + lane - j] : 0.0) + wv_suf + (j == lane ? dA : 0.0);
-                    Bm[j] = act ? sm.HB[j * T + lane] : 0.0;
-                }
             }
             // affine right-hand side: -r_d + G'(lam - W r_p)
             double ra, rdl;
@@ -404,124 +488,101 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                 GT_apply<T>(y, dt, lane, ya, yd);
                 ra = ya - rda; rdl = yd - rdd;
             }
-            // ---- LDL' factorisation, forward solve fused ---------------------------------------------------
-            // Column k is published to shared memory (it is the stored factor AND the broadcast operand of the
-            // rank-1 update); every lane then reads the pivot and forms 1/d_k itself, so no lane-divergent code.
-            // Stores of the cross-block rows by lanes >= T land in the not-yet-written head of column k+1.
-            using SM = WarpSmem<T>;
+            // ---- LDL' of M = H + G'WG, forward solve of the predictor right-hand side fused -------------------
             bool bad = false;
             double inva = 0.0, invd = 0.0;
+            {
+                double R[T], Q[T];                               // accel-block row and cross-block row of this lane
 #pragma unroll
-            for (int k = 0; k < T; ++k) {
-                if (lane >= k && act) sm.L[SM::offL(k) + lane - k] = A[k];
-                sm.L[SM::offL(k) + T + lane - k] = Bm[k];
-                if (lane == k) sm.z[k] = ra;
+                for (int j = 0; j < T; ++j) {
+                    R[j] = act ? sm.HA[SM::offT(j) + lane - j] : 0.0;
+                    Q[j] = act ? sm.HB[j * T + lane] : 0.0;
+                }
                 __syncwarp();
-                const double piv = sm.L[SM::offL(k)];
-                bad = bad || !(piv > 0.0);
-                const double iv = rcp(piv);
-                if (lane == k) { inva = iv; sm.inv[k] = iv; }
-                const double zk = sm.z[k] * iv;
-                const double la = A[k] * iv, lb = Bm[k] * iv;
-                if (lane > k) ra -= A[k] * zk;
-                rdl -= Bm[k] * zk;
-                {
-                    constexpr int dummy = 0; (void)dummy;
-                    int j = k + 1;
-                    if (((SM::offL(k) + j - k) & 1) && j < T) {
-                        const double cj = sm.L[SM::offL(k) + j - k];
-                        A[j] -= la * cj; Bm[j] -= lb * cj; ++j;
-                    }
-#pragma unroll
-                    for (; j + 1 < T; j += 2) {
-                        const double2 cj = *reinterpret_cast<const double2*>(&sm.L[SM::offL(k) + j - k]);
-                        A[j] -= la * cj.x; Bm[j] -= lb * cj.x;
-                        A[j + 1] -= la * cj.y; Bm[j + 1] -= lb * cj.y;
-                    }
-                    if (j < T) {
-                        const double cj = sm.L[SM::offL(k) + j - k];
-                        A[j] -= la * cj; Bm[j] -= lb * cj;
-                    }
-                }
+                int off = 0;
+                constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
+                ldl_accel_steps<T, T - 1>(sm, R, Q, 0, K1, lane, act, wv_suf, dA, ra, rdl, bad, inva, off);
+                ldl_accel_steps<T, T - 1 - K1>(sm, R, Q, K1, K2, lane, act, wv_suf, dA, ra, rdl, bad, inva, off);
+                ldl_accel_steps<T, T - 1 - K2>(sm, R, Q, K2, K3, lane, act, wv_suf, dA, ra, rdl, bad, inva, off);
+                ldl_accel_steps<T, T - 1 - K3>(sm, R, Q, K3, T, lane, act, wv_suf, dA, ra, rdl, bad, inva, off);
             }
-            // steer block: assembled only now (the accel-block rows are dead), then the rank-T update
-            // C -= L21 D^-1 L21' with the cross-block factor rows still in registers
-            double C[T];
+            {
+                // steer block: assembled only now (the accel rows are dead), rank-T update C -= L21 D^-1 L21',
+                // then its own LDL'
+                double C[T];
 #pragma unroll
-            for (int j = 0; j < T; ++j)
-                C[j] = (act ? sm.HC[SM::offT(j) + lane - j] : 0.0) + (j == lane ? dC : 0.0) - (j == lane - 1 ? wr_prev : 0.0);
-            __syncwarp();
-#pragma unroll
-            for (int k = 0; k < T; ++k) {
-                const double lb = Bm[k] * sm.inv[k];
-                int j = 0;
-                if ((SM::offL(k) + T - k) & 1) { C[0] -= lb * sm.L[SM::offL(k) + T - k]; j = 1; }
-#pragma unroll
-                for (; j + 1 < T; j += 2) {
-                    const double2 cj = *reinterpret_cast<const double2*>(&sm.L[SM::offL(k) + T + j - k]);
-                    C[j] -= lb * cj.x; C[j + 1] -= lb * cj.y;
-                }
-                if (j < T) C[j] -= lb * sm.L[SM::offL(k) + T + j - k];
-            }
-#pragma unroll
-            for (int k = 0; k < T; ++k) {
-                if (lane >= k && act) sm.L[SM::offL(T + k) + lane - k] = C[k];
-                if (lane == k) sm.z[T + k] = rdl;
+                for (int j = 0; j < T; ++j) C[j] = act ? sm.HC[SM::offT(j) + lane - j] : 0.0;
                 __syncwarp();
-                const double piv = sm.L[SM::offL(T + k)];
-                bad = bad || !(piv > 0.0);
-                const double iv = rcp(piv);
-                if (lane == k) { invd = iv; sm.inv[T + k] = iv; }
-                const double zk = sm.z[T + k] * iv;
-                const double lc = C[k] * iv;
-                if (lane > k) rdl -= C[k] * zk;
-                int j = k + 1;
-                if (((SM::offL(T + k) + j - k) & 1) && j < T) { C[j] -= lc * sm.L[SM::offL(T + k) + j - k]; ++j; }
+#pragma unroll 1
+                for (int k = 0; k < T; ++k) {
+                    const double lb = act ? sm.LB[k * SM::TSB + lane] * sm.inv[k] : 0.0;
+                    const double* col = &sm.LB[k * SM::TSB];
 #pragma unroll
-                for (; j + 1 < T; j += 2) {
-                    const double2 cj = *reinterpret_cast<const double2*>(&sm.L[SM::offL(T + k) + j - k]);
-                    C[j] -= lc * cj.x; C[j + 1] -= lc * cj.y;
+                    for (int j = 0; j + 1 < T; j += 2) {
+                        const double2 c = *reinterpret_cast<const double2*>(col + j);
+                        C[j] -= lb * c.x; C[j + 1] -= lb * c.y;
+                    }
+                    if (T & 1) C[T - 1] -= lb * col[T - 1];
                 }
-                if (j < T) C[j] -= lc * sm.L[SM::offL(T + k) + j - k];
+                int off = 0;
+                constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
+                ldl_steer_steps<T, T - 1>(sm, C, 0, K1, lane, act, dC, wr_prev, rdl, bad, invd, off);
+                ldl_steer_steps<T, T - 1 - K1>(sm, C, K1, K2, lane, act, dC, wr_prev, rdl, bad, invd, off);
+                ldl_steer_steps<T, T - 1 - K2>(sm, C, K2, K3, lane, act, dC, wr_prev, rdl, bad, invd, off);
+                ldl_steer_steps<T, T - 1 - K3>(sm, C, K3, T, lane, act, dC, wr_prev, rdl, bad, invd, off);
             }
             __syncwarp();
             if (bad) { broke = true; break; }
-
-            // back substitution  L' x = D^-1 z  (column-major factor, AXPY form)
+            // Triangular solves with the pivots in rolled loops.  Lean bodies: unconditional loads from addresses that
+            // are valid for every lane (entries above the diagonal read the tail of the previous column and are
+            // discarded by a predicated FMA), no per-step selects: x_i = (z_i - acc_i) / d_i is formed once, after
+            // the loop, when acc_i has received every x_k, k > i.
+            const int lrow = act ? lane : 0;
+            const int offp_lane = SM::offP(lrow);
+            const double* const LAl = &sm.LA[offp_lane - lrow];      // LAl[k] = (row k, column lane), k > lane
+            const double* const LCl = &sm.LC[offp_lane - lrow];
+            const double* const LBl = &sm.LB[lrow * SM::TSB];        // LBl[k] = (steer row k, accel column lane)
             auto back_solve = [&](double za, double zd, double& xa, double& xd) {
-                const double wa = za * inva, wd = zd * invd;
+                const double wa = za * inva, wd = zd * invd;        // inva = invd = 0 on the idle lanes
                 double accA = 0.0, accD = 0.0;
-                xa = 0.0; xd = 0.0;
-#pragma unroll
+#pragma unroll 4
                 for (int k = T - 1; k >= 0; --k) {
-                    const double xk = shfl(wd - invd * accD, k);
-                    if (lane == k) xd = xk;
-                    if (act) {
-                        if (lane < k) accD += sm.Lat(T + lane, T + k) * xk;
-                        accA += sm.Lat(lane, T + k) * xk;
-                    }
+                    const double xk = shfl(fma(-invd, accD, wd), k);
+                    const double uc = LCl[k], ub = LBl[k];
+                    if (lane < k) accD = fma(uc, xk, accD);
+                    accA = fma(ub, xk, accA);
                 }
-#pragma unroll
-                for (int k = T - 1; k >= 0; --k) {
-                    const double xk = shfl(wa - inva * accA, k);
-                    if (lane == k) xa = xk;
-                    if (act && lane < k) accA += sm.Lat(lane, k) * xk;
+                xd = fma(-invd, accD, wd);
+#pragma unroll 4
+                for (int k = T - 1; k >= 1; --k) {
+                    const double xk = shfl(fma(-inva, accA, wa), k);
+                    const double ua = LAl[k];
+                    if (lane < k) accA = fma(ua, xk, accA);
                 }
+                xa = fma(-inva, accA, wa);
             };
             auto fwd_solve = [&](double& fa, double& fd) {     // L z = r, factor read from shared memory
-#pragma unroll
+                const double* colA = &sm.LA[lrow];             // colA[-k] walks down the packed columns
+                const double* colB = &sm.LB[lrow];
+                int off = 0;
+#pragma unroll 4
                 for (int k = 0; k < T; ++k) {
-                    const double zk = shfl(fa, k) * sm.inv[k];
-                    if (act) {
-                        if (lane > k) fa -= sm.Lat(k, lane) * zk;
-                        fd -= sm.Lat(k, T + lane) * zk;
-                    }
+                    const double zk = shfl(fa * inva, k);
+                    const double ua = colA[off - k], ub = colB[k * SM::TSB];
+                    if (lane > k) fa = fma(-ua, zk, fa);
+                    fd = fma(-ub, zk, fd);
+                    off += (T - k + 1) & ~1;
                 }
-#pragma unroll
-                for (int k = 0; k < T; ++k) {
-                    const double zk = shfl(fd, k) * sm.inv[T + k];
-                    if (act && lane > k) fd -= sm.Lat(T + k, T + lane) * zk;
+                const double* colC = &sm.LC[lrow];
+                off = 0;
+#pragma unroll 4
+                for (int k = 0; k < T - 1; ++k) {
+                    const double zk = shfl(fd * invd, k);
+                    const double uc = colC[off - k];
+                    if (lane > k) fd = fma(-uc, zk, fd);
+                    off += (T - k + 1) & ~1;
                 }
+                if (!act) { fa = 0.0; fd = 0.0; }
             };
 
             // ---- predictor ---------------------------------------------------------------------------------
