@@ -175,7 +175,7 @@ void mpcb_default_config(mpcb_config* c) {
     c->max_steer = 45.0 * (3.141592653589793 / 180.0);      // np.deg2rad(45.0)
     c->max_speed = 30.0 / 3.6; c->min_speed = -5.0; c->r_end = 10.0; c->min_ref_speed = 10 / 3.6;
     c->dt = 0.2; c->wheelbase = 2.86;
-    c->ipm_max_iter = 40; c->ipm_tol_mu = 1e-12; c->ipm_tol_p = 1e-10; c->ipm_tol_d = 1e-9;
+    c->ipm_max_iter = 60; c->ipm_tol_mu = 1e-12; c->ipm_tol_p = 1e-10; c->ipm_tol_d = 1e-9;
     c->car_width = 2.0; c->car_length = 2.86 + 0.64;      // BicycleModelDimensions (car_dimensions.py:82-90)
     c->coupling_horizon = 7.0; c->frame_window = 20;      // mpc_intersection.py:81-82
 }
@@ -406,22 +406,19 @@ namespace {
 
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     switch (h->cfg.T) {
-        case 10: return launch_step<10, 4, 3>(h, p, st);
-        case 13: return launch_step<13, 4, 3>(h, p, st);
+        case 10: return launch_step<10, 1, 8>(h, p, st);
+        case 13: return launch_step<13, 1, 8>(h, p, st);
         case 20:
 #ifdef MPCB_TUNE_VARIANTS
             switch (h->variant) {
-                case 1: return launch_step<20, 4, 3>(h, p, st);
-                case 2: return launch_step<20, 1, 8>(h, p, st);
-                case 3: return launch_step<20, 2, 4>(h, p, st);
+                case 1: return launch_step<20, 4, 2>(h, p, st);
+                case 2: return launch_step<20, 2, 4>(h, p, st);
+                case 3: return launch_step<20, 1, 9>(h, p, st);
                 case 4: return launch_step<20, 1, 12>(h, p, st);
-                case 5: return launch_step<20, 1, 10>(h, p, st);
-                case 6: return launch_step<20, 1, 9>(h, p, st);
-                case 7: return launch_step<20, 1, 14>(h, p, st);
                 default: break;
             }
 #endif
-            return launch_step<20, 4, 2>(h, p, st);
+            return launch_step<20, 1, 8>(h, p, st);
         default: h->err = "mpcb: unsupported horizon"; return MPCB_EINVAL;
     }
 }
