@@ -428,16 +428,23 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
         double gscale, g0a, g0d;
         gradient_scan(0.0, 0.0, g0a, g0d);
         gscale = 1.0 + warp_max(fmax(fabs(g0a), fabs(g0d)));
-        const int offt_lane = WarpSmem<T>::offT(act ? lane : 0);
+        // gradient inside the interior-point loop: g0 + H u from the stored cost Hessian.  Symmetric blocks are
+        // packed lower: entry (lane, j) is column j at row lane for j <= lane, else column lane at row j.
+        const int grow = act ? lane : 0;
+        const double* const hrow = &sm.HA[WarpSmem<T>::offT(grow) - grow];      // hrow[j] = A(j, lane), j > lane
+        const double* const hbr = &sm.HB[grow * T];                              // hbr[j]  = B(lane, j) transposed use
         auto gradient = [&](double a, double d, double& ga, double& gd) {
             double sa = g0a, sd = g0d;
-#pragma unroll 2
+            const double* hcol = &sm.HA[grow];                                   // hcol[-j] after += column length
+            const double* hbc = &sm.HB[grow];
+#pragma unroll 4
             for (int j = 0; j < T; ++j) {
                 const double aj = shfl(a, j), dj = shfl(d, j);
-                const int idx = (j <= lane) ? WarpSmem<T>::offT(j) + lane - j : offt_lane + j - lane;   // symmetric blocks
-                const int row = act ? lane : 0;
-                sa += sm.HA[idx] * aj + sm.HB[row * T + j] * dj;
-                sd += sm.HB[j * T + row] * aj + sm.HC[idx] * dj;
+                const double* pa = (j <= lane) ? hcol - j : hrow + j;
+                const double Aij = pa[0], Cij = pa[WarpSmem<T>::TRI];            // HC follows HA
+                sa = fma(Aij, aj, sa); sa = fma(hbr[j], dj, sa);
+                sd = fma(hbc[0], aj, sd); sd = fma(Cij, dj, sd);
+                hcol += T - j; hbc += T;
             }
             ga = act ? sa : 0.0; gd = act ? sd : 0.0;
         };
@@ -495,8 +502,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                 double R[T], Q[T];                               // accel-block row and cross-block row of this lane
 #pragma unroll
                 for (int j = 0; j < T; ++j) {
-                    R[j] = act ? sm.HA[SM::offT(j) + lane - j] : 0.0;
-                    Q[j] = act ? sm.HB[j * T + lane] : 0.0;
+                    R[j] = sm.HA[SM::offT(j) + lane - j];        // idle lanes read valid memory, their rows are never used
+                    Q[j] = sm.HB[j * T + lane];
                 }
                 __syncwarp();
                 int off = 0;
@@ -511,11 +518,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                 // then its own LDL'
                 double C[T];
 #pragma unroll
-                for (int j = 0; j < T; ++j) C[j] = act ? sm.HC[SM::offT(j) + lane - j] : 0.0;
+                for (int j = 0; j < T; ++j) C[j] = sm.HC[SM::offT(j) + lane - j];
                 __syncwarp();
 #pragma unroll 1
                 for (int k = 0; k < T; ++k) {
-                    const double lb = act ? sm.LB[k * SM::TSB + lane] * sm.inv[k] : 0.0;
+                    const double lb = sm.LB[k * SM::TSB + lane] * sm.inv[k];
                     const double* col = &sm.LB[k * SM::TSB];
 #pragma unroll
                     for (int j = 0; j + 1 < T; j += 2) {
@@ -533,6 +540,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
             }
             __syncwarp();
             if (bad) { broke = true; break; }
+            if (!act) { ra = 0.0; rdl = 0.0; }
             // Triangular solves with the pivots in rolled loops.  Lean bodies: unconditional loads from addresses that
             // are valid for every lane (entries above the diagonal read the tail of the previous column and are
             // discarded by a predicated FMA), no per-step selects: x_i = (z_i - acc_i) / d_i is formed once, after
