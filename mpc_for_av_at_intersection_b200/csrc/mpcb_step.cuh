@@ -35,23 +35,22 @@ template <int T>
 struct WarpSmem {
     static constexpr int N = 2 * T;
     static constexpr int TRI = T * (T + 1) / 2;    // packed lower triangle, column major: (i,j), i >= j, at offT(j) + i - j
-    // factor storage.  Accel / steer blocks: packed lower, every column padded to an even length so that the entry
-    // (row k+j, column k) sits at parity j for every k (aligned 16-byte broadcast loads in a k-rolled loop).
-    // Cross block: full, column stride TSB (even; chosen so that row-wise reads by the back substitution are at
-    // most 2-way bank conflicted).
-    static constexpr int TE = (T + 1) & ~1;
+    // Factor storage: three T x T blocks, column k at colL(k) = k * TSB + (k & 1), row r at + r.  TSB is even and
+    // >= T + 1, so the entry (row k + j, column k) sits at parity j for every k (aligned 16-byte broadcast loads in
+    // a k-rolled loop).  The diagonal and everything above it are stored as ZERO: the triangular solves then run
+    // without a single predicate or select (an update with a zero coefficient is the identity).
+    static constexpr int TE = (T + 2) & ~1;
     static constexpr int TSB = TE + ((TE % 8 == 4) ? 2 : 0);
     __host__ __device__ static constexpr int offT(int j) { return j * T - j * (j - 1) / 2; }
-    __host__ __device__ static constexpr int offP(int k) { return k * T - k * (k - 1) / 2 + ((T & 1) ? (k + 1) / 2 : k / 2); }
-    static constexpr int PTRI = offP(T);
+    __host__ __device__ static constexpr int colL(int k) { return k * TSB + (k & 1); }
     double HA[TRI];                            // cost Hessian, accel block (lower)
     double HC[TRI];                            // steer block (lower)
     double HB[T * T];                          // cross block d/a, [col j][row lane]
-    alignas(16) double LA[PTRI + 32];          // unscaled factor columns of the accel block
+    alignas(16) double LA[T * TSB + 32];       // unscaled factor columns of the accel block (strictly lower, rest 0)
     alignas(16) double LB[T * TSB + 32];       // cross block: column k (accel pivot k), rows = steer stages
-    alignas(16) double LC[PTRI + 32];          // Schur complement (steer block)
+    alignas(16) double LC[T * TSB + 32];       // Schur complement (steer block), same layout as LA
     double inv[N];                             // 1 / d_k
-    double z[N];                               // broadcast slot of the fused forward solve
+    double z[N];                               // broadcast slot of the fused forward solve (already divided by d_k)
     double bc[8][T + 1];                       // per-stage broadcast tables used while assembling H
     double tab[6][T];                          // per-stage model coefficients, re-read by the final prediction
 };
@@ -61,74 +60,73 @@ struct WarpSmem {
 // sm__icc_request_hit_rate 69 %, no_instruction the top stall): a warp keeps its matrix rows in a register window
 // that is SHIFTED by the rank-1 update itself (R[j-1] = R[j] - l * c[j]: the FMA writes one slot down), so the
 // pivot column is always slot 0 and the loop over pivots k is an ordinary loop.  JMAX = trailing columns kept.
+// Critical path of one step: publish column -> barrier -> broadcast loads -> FMAs.  The reciprocal of the NEXT
+// pivot is computed by its owner as soon as the first FMA of the update has produced it, i.e. in the shadow of the
+// remaining FMAs, and published together with the column (a0 / iv carry it from step to step).
 template <int T, int JMAX>
 __device__ __forceinline__ void ldl_accel_steps(WarpSmem<T>& sm, double (&R)[T], double (&Q)[T], int k0, int k1, int lane,
                                                 bool act, double wv_suf, double dA, double& ra, double& rdl, bool& bad,
-                                                double& inva, int& off) {
+                                                double& inva, double& a0, double& ivm) {
     using SM = WarpSmem<T>;
 #pragma unroll 1
     for (int k = k0; k < k1; ++k) {
         const bool mine = lane == k;
-        const double a0 = R[0] + wv_suf + (mine ? dA : 0.0);          // G'WG terms join when the column is published
+        const int col = SM::colL(k);
         const double b0 = Q[0];
-        // lanes >= T store into the not-yet-written columns behind this one (rewritten after the barrier)
-        if (lane >= k) sm.LA[off + lane - k] = a0;
-        sm.LB[k * SM::TSB + lane] = b0;
-        if (mine) sm.z[k] = ra;
+        const double a0s = lane > k ? a0 : 0.0;
+        if (act) { sm.LA[col + lane] = a0s; sm.LB[k * SM::TSB + lane] = b0; }
+        if (mine) { sm.inv[k] = ivm; sm.z[k] = ra * ivm; inva = ivm; bad = bad || !(a0 > 0.0); }
         __syncwarp();
-        const double piv = sm.LA[off];
-        bad = bad || !(piv > 0.0);
-        const double iv = rcp(piv);
-        inva = mine ? iv : inva;
-        if (mine) sm.inv[k] = iv;
-        const double zk = sm.z[k] * iv;
-        const double la = a0 * iv, lb = b0 * iv;
-        if (lane > k) ra -= a0 * zk;
-        rdl -= b0 * zk;
-        if (JMAX >= 1) {
-            const double c1 = sm.LA[off + 1];
-            R[0] = R[1] - la * c1; Q[0] = Q[1] - lb * c1;
-        }
+        const double* pc = &sm.LA[col + k];
+        const double iv = sm.inv[k], zk = sm.z[k];
+        double c[JMAX + 2];
+        c[1] = pc[1];
 #pragma unroll
-        for (int j = 2; j + 1 <= JMAX; j += 2) {
-            const double2 c = *reinterpret_cast<const double2*>(&sm.LA[off + j]);
-            R[j - 1] = R[j] - la * c.x; Q[j - 1] = Q[j] - lb * c.x;
-            R[j] = R[j + 1] - la * c.y; Q[j] = Q[j + 1] - lb * c.y;
+        for (int j = 2; j <= JMAX; j += 2) {
+            const double2 cc = *reinterpret_cast<const double2*>(pc + j);
+            c[j] = cc.x; c[j + 1] = cc.y;
         }
-        if (JMAX >= 2 && (JMAX % 2) == 0) {
-            const double c = sm.LA[off + JMAX];
-            R[JMAX - 1] = R[JMAX] - la * c; Q[JMAX - 1] = Q[JMAX] - lb * c;
-        }
-        off += (T - k + 1) & ~1;
+        const double la = a0s * iv, lb = b0 * iv;
+        ra = fma(-a0s, zk, ra);
+        rdl = fma(-b0, zk, rdl);
+        R[0] = R[1] - la * c[1];
+        a0 = R[0] + wv_suf + (lane == k + 1 ? dA : 0.0);           // G'WG terms join when the column is published
+        ivm = rcp(a0);
+        Q[0] = Q[1] - lb * c[1];
+#pragma unroll
+        for (int j = 2; j <= JMAX; ++j) { R[j - 1] = R[j] - la * c[j]; Q[j - 1] = Q[j] - lb * c[j]; }
     }
 }
 
 template <int T, int JMAX>
 __device__ __forceinline__ void ldl_steer_steps(WarpSmem<T>& sm, double (&C)[T], int k0, int k1, int lane, bool act,
-                                                double dC, double wr_prev, double& rdl, bool& bad, double& invd, int& off) {
+                                                double dC, double wr_prev, double& rdl, bool& bad, double& invd,
+                                                double& c0, double& ivm) {
+    using SM = WarpSmem<T>;
 #pragma unroll 1
     for (int k = k0; k < k1; ++k) {
         const bool mine = lane == k;
-        const double c0 = C[0] + (mine ? dC : 0.0) - (lane == k + 1 ? wr_prev : 0.0);
-        if (lane >= k) sm.LC[off + lane - k] = c0;
-        if (mine) sm.z[T + k] = rdl;
+        const int col = SM::colL(k);
+        const double c0s = lane > k ? c0 : 0.0;
+        if (act) sm.LC[col + lane] = c0s;
+        if (mine) { sm.inv[T + k] = ivm; sm.z[T + k] = rdl * ivm; invd = ivm; bad = bad || !(c0 > 0.0); }
         __syncwarp();
-        const double piv = sm.LC[off];
-        bad = bad || !(piv > 0.0);
-        const double iv = rcp(piv);
-        invd = mine ? iv : invd;
-        const double zk = sm.z[T + k] * iv;
-        const double lc = c0 * iv;
-        if (lane > k) rdl -= c0 * zk;
-        if (JMAX >= 1) C[0] = C[1] - lc * sm.LC[off + 1];
+        const double* pc = &sm.LC[col + k];
+        const double iv = sm.inv[T + k], zk = sm.z[T + k];
+        double c[JMAX + 2];
+        c[1] = pc[1];
 #pragma unroll
-        for (int j = 2; j + 1 <= JMAX; j += 2) {
-            const double2 c = *reinterpret_cast<const double2*>(&sm.LC[off + j]);
-            C[j - 1] = C[j] - lc * c.x;
-            C[j] = C[j + 1] - lc * c.y;
+        for (int j = 2; j <= JMAX; j += 2) {
+            const double2 cc = *reinterpret_cast<const double2*>(pc + j);
+            c[j] = cc.x; c[j + 1] = cc.y;
         }
-        if (JMAX >= 2 && (JMAX % 2) == 0) C[JMAX - 1] = C[JMAX] - lc * sm.LC[off + JMAX];
-        off += (T - k + 1) & ~1;
+        const double lc = c0s * iv;
+        rdl = fma(-c0s, zk, rdl);
+        C[0] = C[1] - lc * c[1];
+        c0 = C[0] + (lane == k + 1 ? dC : 0.0) - (lane == k + 2 ? wr_prev : 0.0);
+        ivm = rcp(c0);
+#pragma unroll
+        for (int j = 2; j <= JMAX; ++j) C[j - 1] = C[j] - lc * c[j];
     }
 }
 
@@ -505,13 +503,14 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                     R[j] = sm.HA[SM::offT(j) + lane - j];        // idle lanes read valid memory, their rows are never used
                     Q[j] = sm.HB[j * T + lane];
                 }
+                double a0 = R[0] + wv_suf + (lane == 0 ? dA : 0.0);
+                double ivm = rcp(a0);
                 __syncwarp();
-                int off = 0;
                 constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
-                ldl_accel_steps<T, T - 1>(sm, R, Q, 0, K1, lane, act, wv_suf, dA, ra, rdl, bad, inva, off);
-                ldl_accel_steps<T, T - 1 - K1>(sm, R, Q, K1, K2, lane, act, wv_suf, dA, ra, rdl, bad, inva, off);
-                ldl_accel_steps<T, T - 1 - K2>(sm, R, Q, K2, K3, lane, act, wv_suf, dA, ra, rdl, bad, inva, off);
-                ldl_accel_steps<T, T - 1 - K3>(sm, R, Q, K3, T, lane, act, wv_suf, dA, ra, rdl, bad, inva, off);
+                ldl_accel_steps<T, T - 1>(sm, R, Q, 0, K1, lane, act, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
+                ldl_accel_steps<T, T - 1 - K1>(sm, R, Q, K1, K2, lane, act, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
+                ldl_accel_steps<T, T - 1 - K2>(sm, R, Q, K2, K3, lane, act, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
+                ldl_accel_steps<T, T - 1 - K3>(sm, R, Q, K3, T, lane, act, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
             }
             {
                 // steer block: assembled only now (the accel rows are dead), rank-T update C -= L21 D^-1 L21',
@@ -531,66 +530,62 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                     }
                     if (T & 1) C[T - 1] -= lb * col[T - 1];
                 }
-                int off = 0;
+                double c0 = C[0] + (lane == 0 ? dC : 0.0) - (lane == 1 ? wr_prev : 0.0);
+                double ivm = rcp(c0);
                 constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
-                ldl_steer_steps<T, T - 1>(sm, C, 0, K1, lane, act, dC, wr_prev, rdl, bad, invd, off);
-                ldl_steer_steps<T, T - 1 - K1>(sm, C, K1, K2, lane, act, dC, wr_prev, rdl, bad, invd, off);
-                ldl_steer_steps<T, T - 1 - K2>(sm, C, K2, K3, lane, act, dC, wr_prev, rdl, bad, invd, off);
-                ldl_steer_steps<T, T - 1 - K3>(sm, C, K3, T, lane, act, dC, wr_prev, rdl, bad, invd, off);
+                ldl_steer_steps<T, T - 1>(sm, C, 0, K1, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
+                ldl_steer_steps<T, T - 1 - K1>(sm, C, K1, K2, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
+                ldl_steer_steps<T, T - 1 - K2>(sm, C, K2, K3, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
+                ldl_steer_steps<T, T - 1 - K3>(sm, C, K3, T, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
             }
             __syncwarp();
-            if (bad) { broke = true; break; }
+            if (__any_sync(MPCB_FULL, bad)) { broke = true; break; }
             if (!act) { ra = 0.0; rdl = 0.0; }
-            // Triangular solves with the pivots in rolled loops.  Lean bodies: unconditional loads from addresses that
-            // are valid for every lane (entries above the diagonal read the tail of the previous column and are
-            // discarded by a predicated FMA), no per-step selects: x_i = (z_i - acc_i) / d_i is formed once, after
-            // the loop, when acc_i has received every x_k, k > i.
+            // Triangular solves with the pivots in rolled loops.  The factor blocks are zero on and above the diagonal,
+            // so every step is shuffle -> FMA with no predicate; the running right-hand sides are kept PRE-SCALED by
+            // 1/d_i (the coefficient is scaled instead, off the dependency chain), which makes the value a lane
+            // broadcasts at its own step the finished unknown.
             const int lrow = act ? lane : 0;
-            const int offp_lane = SM::offP(lrow);
-            const double* const LAl = &sm.LA[offp_lane - lrow];      // LAl[k] = (row k, column lane), k > lane
-            const double* const LCl = &sm.LC[offp_lane - lrow];
-            const double* const LBl = &sm.LB[lrow * SM::TSB];        // LBl[k] = (steer row k, accel column lane)
-            auto back_solve = [&](double za, double zd, double& xa, double& xd) {
-                const double wa = za * inva, wd = zd * invd;        // inva = invd = 0 on the idle lanes
-                double accA = 0.0, accD = 0.0;
+            const double* const LAr = &sm.LA[SM::colL(lrow)];        // LAr[k] = (row k, column lane)
+            const double* const LCr = &sm.LC[SM::colL(lrow)];
+            const double* const LBr = &sm.LB[lrow * SM::TSB];        // LBr[k] = (steer row k, accel column lane)
+            auto back_solve = [&](double ha, double hd, double& xa, double& xd) {      // L' x = h, h = D^-1 z
 #pragma unroll 4
                 for (int k = T - 1; k >= 0; --k) {
-                    const double xk = shfl(fma(-invd, accD, wd), k);
-                    const double uc = LCl[k], ub = LBl[k];
-                    if (lane < k) accD = fma(uc, xk, accD);
-                    accA = fma(ub, xk, accA);
+                    const double xk = shfl(hd, k);
+                    const double uc = LCr[k] * invd, ub = LBr[k] * inva;
+                    hd = fma(-uc, xk, hd);
+                    ha = fma(-ub, xk, ha);
                 }
-                xd = fma(-invd, accD, wd);
+                xd = hd;
 #pragma unroll 4
                 for (int k = T - 1; k >= 1; --k) {
-                    const double xk = shfl(fma(-inva, accA, wa), k);
-                    const double ua = LAl[k];
-                    if (lane < k) accA = fma(ua, xk, accA);
+                    const double xk = shfl(ha, k);
+                    const double ua = LAr[k] * inva;
+                    ha = fma(-ua, xk, ha);
                 }
-                xa = fma(-inva, accA, wa);
+                xa = ha;
             };
-            auto fwd_solve = [&](double& fa, double& fd) {     // L z = r, factor read from shared memory
-                const double* colA = &sm.LA[lrow];             // colA[-k] walks down the packed columns
+            auto fwd_solve = [&](double& fa, double& fd) {     // L z = r, factor read from shared memory; returns D^-1-free z
+                const double* colA = &sm.LA[lrow];
                 const double* colB = &sm.LB[lrow];
-                int off = 0;
+                double ga = fa * inva;
 #pragma unroll 4
                 for (int k = 0; k < T; ++k) {
-                    const double zk = shfl(fa * inva, k);
-                    const double ua = colA[off - k], ub = colB[k * SM::TSB];
-                    if (lane > k) fa = fma(-ua, zk, fa);
+                    const double zk = shfl(ga, k);
+                    const double ua = colA[SM::colL(k)] * inva, ub = colB[k * SM::TSB];
+                    ga = fma(-ua, zk, ga);
                     fd = fma(-ub, zk, fd);
-                    off += (T - k + 1) & ~1;
                 }
                 const double* colC = &sm.LC[lrow];
-                off = 0;
+                double gd = fd * invd;
 #pragma unroll 4
                 for (int k = 0; k < T - 1; ++k) {
-                    const double zk = shfl(fd * invd, k);
-                    const double uc = colC[off - k];
-                    if (lane > k) fd = fma(-uc, zk, fd);
-                    off += (T - k + 1) & ~1;
+                    const double zk = shfl(gd, k);
+                    const double uc = colC[SM::colL(k)] * invd;
+                    gd = fma(-uc, zk, gd);
                 }
-                if (!act) { fa = 0.0; fd = 0.0; }
+                fa = ga; fd = gd;                              // = D^-1 L^-1 r
             };
 
             // ---- predictor ---------------------------------------------------------------------------------
@@ -598,7 +593,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
             double sigma_mu;
             {
                 double da, dd, g[8];
-                back_solve(ra, rdl, da, dd);
+                back_solve(ra * inva, rdl * invd, da, dd);                   // inva = invd = 0 on the idle lanes
                 G_apply<T>(da, dd, dt, lane, g);
                 double tmax = 0.0;
 #pragma unroll

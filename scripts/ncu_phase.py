@@ -1,0 +1,33 @@
+import re,csv,sys
+from collections import defaultdict
+sass, prof = sys.argv[1], sys.argv[2]
+cur=None; inst_line=[]; ops=[]
+for ln in open(sass):
+    if '//## File' in ln:
+        ms=re.findall(r'File "([^"]+)", line (\d+)',ln)
+        pick=None
+        for f,l in ms:
+            if f.endswith('mpcb_step.cuh'): pick=int(l)
+        cur=pick if pick else cur; continue
+    m=re.match(r'\s+/\*[0-9a-f]{4,}\*/\s+(@!?U?P\d\s+)?([A-Z0-9_.]+)',ln)
+    if m: inst_line.append(cur); ops.append(m.group(2).split('.')[0])
+rows=list(csv.reader(open(prof)))
+hdr=rows[1]; ix={h:i for i,h in enumerate(hdr)}
+data=[r for r in rows[2:] if len(r)==len(hdr) and r[0]!='Address']
+assert len(data)==len(inst_line),(len(data),len(inst_line))
+src=open('/root/repo/mpc_for_av_at_intersection_b200/csrc/mpcb_step.cuh').read().split('\n')
+def find(s): return next(i+1 for i,l in enumerate(src) if s in l)
+marks=sorted([(1,'file head'),(find('void ldl_accel_steps'),'ldl accel steps'),(find('void ldl_steer_steps'),'ldl steer steps'),(find('top-3 insertion'),'nearest idx'),(find('structured constraint operator'),'G ops'),(find('__global__ void'),'kernel head/inputs'),(find('A2: reference lookup'),'A2'),(find('A3: rollout'),'A3'),(find('A4: linearisation'),'A4/A5'),(find('condensed Hessian from suffix'),'H build'),(find('linear prediction and objective gradient'),'predict/grad defs'),(find('A6: interior point'),'ipm init + grad matvec'),(find('for (; feasible0; ++it)'),'residuals'),(find("M = H + G' W G"),'W, rhs'),(find("LDL' of M = H"),'factor driver+syrk'),(find('Triangular solves with the pivots'),'solves'),(find('---- predictor'),'predictor'),(find('---- corrector'),'corrector'),(find('iters = it;'),'epilogue')])
+agg=defaultdict(lambda:[0,0,0,defaultdict(int)])
+for l,op,r in zip(inst_line,ops,data):
+    name='?'
+    for start,n in marks:
+        if l and l>=start: name=n
+    g=agg[name]; ex=int(r[ix['Instructions Executed']]); g[0]+=int(r[ix['# Samples']]); g[1]+=ex; g[2]+=1; g[3][op]+=ex
+ts=sum(a[0] for a in agg.values()); ti=sum(a[1] for a in agg.values())
+NP=float(sys.argv[3]) if len(sys.argv)>3 else 4096
+print('total exec/problem', ti/NP)
+for start,n in marks:
+    g=agg[n]
+    top=sorted(g[3].items(), key=lambda kv:-kv[1])[:7]
+    print(f"{start:4d} {n:24s} smp {g[0]/ts:.3f} exec {g[1]/NP:7.0f} ({g[1]/ti:.3f}) static {g[2]:5d}  "+' '.join(f"{k}:{v/NP:.0f}" for k,v in top))
