@@ -126,12 +126,30 @@ constexpr int kHorizons[] = {10, 13, 20};
 template <int T, int WARPS, int MINB>
 int launch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     const size_t smem = sizeof(mpcb::WarpSmem<T>) * WARPS;
-    auto kern = mpcb::mpc_step_kernel<T, WARPS, MINB>;
+    void (*kern)(const StepParams);
+    if constexpr (MINB > 32) kern = mpcb::mpc_step_kernel_r<T, WARPS, MINB>;
+    else kern = mpcb::mpc_step_kernel<T, WARPS, MINB>;
     static thread_local int configured_dev = -1;
     if (configured_dev != h->device) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         configured_dev = h->device;
+#ifdef MPCB_TUNE_VARIANTS
+        if (getenv("MPCB_SHOW_OCCUPANCY")) {
+            int nb = 0;
+            cudaFuncAttributes fa;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, WARPS * 32, smem);
+            cudaFuncGetAttributes(&fa, kern);
+            int nb0 = 0, nbh = 0, smsm = 0, regsm = 0;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb0, kern, WARPS * 32, 0);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nbh, kern, WARPS * 32, smem / 2);
+            cudaDeviceGetAttribute(&smsm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, h->device);
+            cudaDeviceGetAttribute(&regsm, cudaDevAttrMaxRegistersPerMultiprocessor, h->device);
+            fprintf(stderr, "mpcb: smem/SM=%d regs/SM=%d CTAs/SM with smem 0: %d, smem/2: %d\n", smsm, regsm, nb0, nbh);
+            fprintf(stderr, "mpcb: T=%d warps/CTA=%d bound=%d regs=%d smem/CTA=%zu local=%zu resident CTAs/SM=%d\n", T, WARPS, MINB,
+                    fa.numRegs, smem, (size_t)fa.localSizeBytes, nb);
+        }
+#endif
     }
     const int grid = (p.B + WARPS - 1) / WARPS;
     kern<<<grid, WARPS * 32, smem, st>>>(p);
@@ -407,14 +425,22 @@ namespace {
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     switch (h->cfg.T) {
         case 10: return launch_step<10, 1, 8>(h, p, st);
-        case 13: return launch_step<13, 1, 8>(h, p, st);
+        case 13:
+#ifdef MPCB_TUNE_VARIANTS
+            switch (h->variant) {
+                case 1: return launch_step<13, 1, 168>(h, p, st);
+                case 2: return launch_step<13, 1, 128>(h, p, st);
+                default: break;
+            }
+#endif
+            return launch_step<13, 1, 8>(h, p, st);
         case 20:
 #ifdef MPCB_TUNE_VARIANTS
             switch (h->variant) {
-                case 1: return launch_step<20, 4, 2>(h, p, st);
-                case 2: return launch_step<20, 2, 4>(h, p, st);
-                case 3: return launch_step<20, 1, 9>(h, p, st);
-                case 4: return launch_step<20, 1, 12>(h, p, st);
+                case 1: return launch_step<20, 1, 200>(h, p, st);
+                case 2: return launch_step<20, 1, 184>(h, p, st);
+                case 3: return launch_step<20, 1, 224>(h, p, st);
+                case 4: return launch_step<20, 1, 168>(h, p, st);
                 default: break;
             }
 #endif

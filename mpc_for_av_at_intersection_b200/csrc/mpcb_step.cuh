@@ -22,6 +22,8 @@
 // lane publishes its (unscaled) column-k entry to shared memory, which is at the same time the
 // broadcast buffer of the rank-1 update and the column-major factor used by the triangular solves.
 #pragma once
+#include <type_traits>
+
 #include "mpcb_common.cuh"
 
 #define MPCB_ST_OPTIMAL 0
@@ -34,23 +36,28 @@ namespace mpcb {
 template <int T>
 struct WarpSmem {
     static constexpr int N = 2 * T;
-    static constexpr int TRI = T * (T + 1) / 2;    // packed lower triangle, column major: (i,j), i >= j, at offT(j) + i - j
-    // Factor storage: three T x T blocks, column k at colL(k) = k * TSB + (k & 1), row r at + r.  TSB is even and
-    // >= T + 1, so the entry (row k + j, column k) sits at parity j for every k (aligned 16-byte broadcast loads in
-    // a k-rolled loop).  The diagonal and everything above it are stored as ZERO: the triangular solves then run
-    // without a single predicate or select (an update with a zero coefficient is the identity).
-    static constexpr int TE = (T + 2) & ~1;
-    static constexpr int TSB = TE + ((TE % 8 == 4) ? 2 : 0);
-    __host__ __device__ static constexpr int offT(int j) { return j * T - j * (j - 1) / 2; }
-    __host__ __device__ static constexpr int colL(int k) { return k * TSB + (k & 1); }
-    double HA[TRI];                            // cost Hessian, accel block (lower)
-    double HC[TRI];                            // steer block (lower)
-    double HB[T * T];                          // cross block d/a, [col j][row lane]
-    alignas(16) double LA[T * TSB + 32];       // unscaled factor columns of the accel block (strictly lower, rest 0)
-    alignas(16) double LB[T * TSB + 32];       // cross block: column k (accel pivot k), rows = steer stages
-    alignas(16) double LC[T * TSB + 32];       // Schur complement (steer block), same layout as LA
-    double inv[N];                             // 1 / d_k
-    double z[N];                               // broadcast slot of the fused forward solve (already divided by d_k)
+    // Every T x T block is stored column-major with a column stride S = 2 * odd and a small per-column shift, chosen
+    // so that BOTH access directions are bank-conflict free for 8-byte loads: down a column (consecutive lanes,
+    // consecutive words) and along a row (lane i reads column i: i * S + shift(i) covers all 16 8-byte bank pairs
+    // over any 16 consecutive i).  Idle lanes alias rows 4..15 (lane & 15) and hit the same words as live lanes.
+    //   cost Hessian blocks and the cross factor:   colB(k) = k * SB + ((k >> 3) & 1)
+    //   accel / steer factor blocks:                colL(k) = k * SA + (k & 1) + 2 * ((k >> 3) & 1)
+    // colL keeps the entry (row k + j, column k) at parity j for every k (aligned 16-byte broadcast loads in a
+    // k-rolled loop).  The factor blocks are ZERO on and above the diagonal: the triangular solves then run without
+    // a predicate or select (an update with a zero coefficient is the identity).
+    __host__ __device__ static constexpr int stride_2odd(int lo) { int s = (lo + 1) & ~1; return (s / 2) % 2 ? s : s + 2; }
+    static constexpr int SB = stride_2odd(T + 1);
+    static constexpr int SA = stride_2odd(T + 3);
+    __host__ __device__ static constexpr int colB(int k) { return k * SB + ((k >> 3) & 1); }
+    __host__ __device__ static constexpr int colL(int k) { return k * SA + (k & 1) + 2 * ((k >> 3) & 1); }
+    double HA[T * SB + 2];                     // cost Hessian, accel block (full, symmetric)
+    double HC[T * SB + 2];                     // steer block (full, symmetric)
+    double HB[T * SB + 2];                     // cross block: column j = accel index, row = steer stage
+    alignas(16) double LA[T * SA + 36];        // unscaled factor columns of the accel block (strictly lower, rest 0)
+    alignas(16) double LB[T * SB + 36];        // cross block: column k (accel pivot k), rows = steer stages
+    alignas(16) double LC[T * SA + 36];        // Schur complement (steer block), same layout as LA
+    double inv[N + 32];                        // 1 / d_k (+ one scratch slot per lane: branch-free publish)
+    double z[N + 32];                               // broadcast slot of the fused forward solve (already divided by d_k)
     double bc[8][T + 1];                       // per-stage broadcast tables used while assembling H
     double tab[6][T];                          // per-stage model coefficients, re-read by the final prediction
 };
@@ -65,7 +72,7 @@ struct WarpSmem {
 // remaining FMAs, and published together with the column (a0 / iv carry it from step to step).
 template <int T, int JMAX>
 __device__ __forceinline__ void ldl_accel_steps(WarpSmem<T>& sm, double (&R)[T], double (&Q)[T], int k0, int k1, int lane,
-                                                bool act, double wv_suf, double dA, double& ra, double& rdl, bool& bad,
+                                                double wv_suf, double dA, double& ra, double& rdl, bool& bad,
                                                 double& inva, double& a0, double& ivm) {
     using SM = WarpSmem<T>;
 #pragma unroll 1
@@ -74,8 +81,13 @@ __device__ __forceinline__ void ldl_accel_steps(WarpSmem<T>& sm, double (&R)[T],
         const int col = SM::colL(k);
         const double b0 = Q[0];
         const double a0s = lane > k ? a0 : 0.0;
-        if (act) { sm.LA[col + lane] = a0s; sm.LB[k * SM::TSB + lane] = b0; }
-        if (mine) { sm.inv[k] = ivm; sm.z[k] = ra * ivm; inva = ivm; bad = bad || !(a0 > 0.0); }
+        // branch-free publish: idle lanes (>= T) write behind the column, into rows of column k + 1 that step k + 1
+        // rewrites (or into the pad after the last column); lanes other than k write their own scratch slot
+        sm.LA[col + lane] = a0s; sm.LB[SM::colB(k) + lane] = b0;
+        const int slot = mine ? k : SM::N + lane;
+        sm.inv[slot] = ivm; sm.z[slot] = ra * ivm;
+        inva = mine ? ivm : inva;
+        bad = bad || (mine && !(a0 > 0.0));
         __syncwarp();
         const double* pc = &sm.LA[col + k];
         const double iv = sm.inv[k], zk = sm.z[k];
@@ -108,8 +120,11 @@ __device__ __forceinline__ void ldl_steer_steps(WarpSmem<T>& sm, double (&C)[T],
         const bool mine = lane == k;
         const int col = SM::colL(k);
         const double c0s = lane > k ? c0 : 0.0;
-        if (act) sm.LC[col + lane] = c0s;
-        if (mine) { sm.inv[T + k] = ivm; sm.z[T + k] = rdl * ivm; invd = ivm; bad = bad || !(c0 > 0.0); }
+        sm.LC[col + lane] = c0s;
+        const int slot = mine ? T + k : SM::N + lane;
+        sm.inv[slot] = ivm; sm.z[slot] = rdl * ivm;
+        invd = mine ? ivm : invd;
+        bad = bad || (mine && !(c0 > 0.0));
         __syncwarp();
         const double* pc = &sm.LC[col + k];
         const double iv = sm.inv[T + k], zk = sm.z[T + k];
@@ -202,8 +217,8 @@ __device__ __forceinline__ void GT_apply(const double (&y)[8], double dt, int la
     gd = y[2] - y[3] - r + shfl_up1(r, lane);
 }
 
-template <int T, int WARPS, int MINB>
-__global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepParams p) {
+template <int T, int WARPS>
+__device__ __forceinline__ void mpc_step_body(const StepParams& p) {
     static_assert(T >= 3 && T <= 31, "one warp per problem needs T+1 <= 32");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -353,8 +368,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                 if (j == lane) { Aij += 2.0 * ra_w + 2.0 * p.Rd0 * nb; Cij += 2.0 * rd_w + 2.0 * p.Rd1 * nb; }
                 if (j == lane - 1) { Aij -= 2.0 * p.Rd0; Cij -= 2.0 * p.Rd1; }
                 if (act) {
-                    sm.HB[j * T + lane] = Bij;
-                    if (j <= lane) { sm.HA[WarpSmem<T>::offT(j) + lane - j] = Aij; sm.HC[WarpSmem<T>::offT(j) + lane - j] = Cij; }
+                    sm.HB[WarpSmem<T>::colB(j) + lane] = Bij;
+                    if (j <= lane) {                             // symmetric blocks: both triangles are stored
+                        sm.HA[WarpSmem<T>::colB(j) + lane] = Aij; sm.HC[WarpSmem<T>::colB(j) + lane] = Cij;
+                        sm.HA[WarpSmem<T>::colB(lane) + j] = Aij; sm.HC[WarpSmem<T>::colB(lane) + j] = Cij;
+                    }
                 }
             }
             __syncwarp();
@@ -426,23 +444,19 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
         double gscale, g0a, g0d;
         gradient_scan(0.0, 0.0, g0a, g0d);
         gscale = 1.0 + warp_max(fmax(fabs(g0a), fabs(g0d)));
-        // gradient inside the interior-point loop: g0 + H u from the stored cost Hessian.  Symmetric blocks are
-        // packed lower: entry (lane, j) is column j at row lane for j <= lane, else column lane at row j.
-        const int grow = act ? lane : 0;
-        const double* const hrow = &sm.HA[WarpSmem<T>::offT(grow) - grow];      // hrow[j] = A(j, lane), j > lane
-        const double* const hbr = &sm.HB[grow * T];                              // hbr[j]  = B(lane, j) transposed use
+        // gradient inside the interior-point loop: g0 + H u from the stored cost Hessian (column j of every block is
+        // read down the lanes; the transposed cross block along row `lane`)
+        const int grow = act ? lane : (lane & 15);
         auto gradient = [&](double a, double d, double& ga, double& gd) {
+            using SMg = WarpSmem<T>;
             double sa = g0a, sd = g0d;
-            const double* hcol = &sm.HA[grow];                                   // hcol[-j] after += column length
-            const double* hbc = &sm.HB[grow];
-#pragma unroll 4
+            const double* const hbr = &sm.HB[SMg::colB(grow)];                   // hbr[j] = B(steer j, accel lane)
+#pragma unroll
             for (int j = 0; j < T; ++j) {
                 const double aj = shfl(a, j), dj = shfl(d, j);
-                const double* pa = (j <= lane) ? hcol - j : hrow + j;
-                const double Aij = pa[0], Cij = pa[WarpSmem<T>::TRI];            // HC follows HA
-                sa = fma(Aij, aj, sa); sa = fma(hbr[j], dj, sa);
-                sd = fma(hbc[0], aj, sd); sd = fma(Cij, dj, sd);
-                hcol += T - j; hbc += T;
+                const int cj = SMg::colB(j) + grow;
+                sa = fma(sm.HA[cj], aj, sa); sa = fma(hbr[j], dj, sa);
+                sd = fma(sm.HB[cj], aj, sd); sd = fma(sm.HC[cj], dj, sd);
             }
             ga = act ? sa : 0.0; gd = act ? sd : 0.0;
         };
@@ -499,37 +513,44 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
             {
                 double R[T], Q[T];                               // accel-block row and cross-block row of this lane
 #pragma unroll
-                for (int j = 0; j < T; ++j) {
-                    R[j] = sm.HA[SM::offT(j) + lane - j];        // idle lanes read valid memory, their rows are never used
-                    Q[j] = sm.HB[j * T + lane];
+                for (int j = 0; j < T; ++j) {                    // idle lanes read valid memory, their rows are never used
+                    R[j] = sm.HA[SM::colB(j) + lane];
+                    Q[j] = sm.HB[SM::colB(j) + lane];
                 }
                 double a0 = R[0] + wv_suf + (lane == 0 ? dA : 0.0);
                 double ivm = rcp(a0);
                 __syncwarp();
                 constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
-                ldl_accel_steps<T, T - 1>(sm, R, Q, 0, K1, lane, act, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
-                ldl_accel_steps<T, T - 1 - K1>(sm, R, Q, K1, K2, lane, act, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
-                ldl_accel_steps<T, T - 1 - K2>(sm, R, Q, K2, K3, lane, act, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
-                ldl_accel_steps<T, T - 1 - K3>(sm, R, Q, K3, T, lane, act, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
+                ldl_accel_steps<T, T - 1>(sm, R, Q, 0, K1, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
+                ldl_accel_steps<T, T - 1 - K1>(sm, R, Q, K1, K2, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
+                ldl_accel_steps<T, T - 1 - K2>(sm, R, Q, K2, K3, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
+                ldl_accel_steps<T, T - 1 - K3>(sm, R, Q, K3, T, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
             }
             {
                 // steer block: assembled only now (the accel rows are dead), rank-T update C -= L21 D^-1 L21',
                 // then its own LDL'
                 double C[T];
 #pragma unroll
-                for (int j = 0; j < T; ++j) C[j] = sm.HC[SM::offT(j) + lane - j];
+                for (int j = 0; j < T; ++j) C[j] = sm.HC[SM::colB(j) + lane];
                 __syncwarp();
+                auto syrk = [&](int k0, int k1, auto odd_base) {          // columns with an odd base shift the pairs
+                    constexpr bool ODD = decltype(odd_base)::value;
 #pragma unroll 1
-                for (int k = 0; k < T; ++k) {
-                    const double lb = sm.LB[k * SM::TSB + lane] * sm.inv[k];
-                    const double* col = &sm.LB[k * SM::TSB];
+                    for (int k = k0; k < k1; ++k) {
+                        const double* col = &sm.LB[k * SM::SB + (ODD ? 1 : 0)];
+                        const double lb = col[lane] * sm.inv[k];
+                        if (ODD) C[0] -= lb * col[0];
 #pragma unroll
-                    for (int j = 0; j + 1 < T; j += 2) {
-                        const double2 c = *reinterpret_cast<const double2*>(col + j);
-                        C[j] -= lb * c.x; C[j + 1] -= lb * c.y;
+                        for (int j = ODD ? 1 : 0; j + 1 < T; j += 2) {
+                            const double2 c = *reinterpret_cast<const double2*>(col + j);
+                            C[j] -= lb * c.x; C[j + 1] -= lb * c.y;
+                        }
+                        if (((T - (ODD ? 1 : 0)) & 1)) C[T - 1] -= lb * col[T - 1];
                     }
-                    if (T & 1) C[T - 1] -= lb * col[T - 1];
-                }
+                };
+                syrk(0, T < 8 ? T : 8, std::false_type{});
+                if (T > 8) syrk(8, T < 16 ? T : 16, std::true_type{});
+                if (T > 16) syrk(16, T, std::false_type{});
                 double c0 = C[0] + (lane == 0 ? dC : 0.0) - (lane == 1 ? wr_prev : 0.0);
                 double ivm = rcp(c0);
                 constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
@@ -545,12 +566,12 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
             // so every step is shuffle -> FMA with no predicate; the running right-hand sides are kept PRE-SCALED by
             // 1/d_i (the coefficient is scaled instead, off the dependency chain), which makes the value a lane
             // broadcasts at its own step the finished unknown.
-            const int lrow = act ? lane : 0;
+            const int lrow = act ? lane : (lane & 15);
             const double* const LAr = &sm.LA[SM::colL(lrow)];        // LAr[k] = (row k, column lane)
             const double* const LCr = &sm.LC[SM::colL(lrow)];
-            const double* const LBr = &sm.LB[lrow * SM::TSB];        // LBr[k] = (steer row k, accel column lane)
+            const double* const LBr = &sm.LB[SM::colB(lrow)];        // LBr[k] = (steer row k, accel column lane)
             auto back_solve = [&](double ha, double hd, double& xa, double& xd) {      // L' x = h, h = D^-1 z
-#pragma unroll 4
+#pragma unroll
                 for (int k = T - 1; k >= 0; --k) {
                     const double xk = shfl(hd, k);
                     const double uc = LCr[k] * invd, ub = LBr[k] * inva;
@@ -558,7 +579,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                     ha = fma(-ub, xk, ha);
                 }
                 xd = hd;
-#pragma unroll 4
+#pragma unroll
                 for (int k = T - 1; k >= 1; --k) {
                     const double xk = shfl(ha, k);
                     const double ua = LAr[k] * inva;
@@ -570,16 +591,16 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
                 const double* colA = &sm.LA[lrow];
                 const double* colB = &sm.LB[lrow];
                 double ga = fa * inva;
-#pragma unroll 4
+#pragma unroll
                 for (int k = 0; k < T; ++k) {
                     const double zk = shfl(ga, k);
-                    const double ua = colA[SM::colL(k)] * inva, ub = colB[k * SM::TSB];
+                    const double ua = colA[SM::colL(k)] * inva, ub = colB[SM::colB(k)];
                     ga = fma(-ua, zk, ga);
                     fd = fma(-ub, zk, fd);
                 }
                 const double* colC = &sm.LC[lrow];
                 double gd = fd * invd;
-#pragma unroll 4
+#pragma unroll
                 for (int k = 0; k < T - 1; ++k) {
                     const double zk = shfl(gd, k);
                     const double uc = colC[SM::colL(k)] * invd;
@@ -730,5 +751,13 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepPa
         if (p.history && lane < 8) p.history[8 * (size_t)b + lane] = col;
     }
 }
+
+// Register budget: REGS <= 32 is a minimum-resident-CTA hint (__launch_bounds__), REGS > 32 an explicit cap per
+// thread (__maxnreg__; ptxas quantises the launch-bounds form much more coarsely than the hardware allocates).
+template <int T, int WARPS, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepParams p) { mpc_step_body<T, WARPS>(p); }
+
+template <int T, int WARPS, int REGS>
+__global__ void __maxnreg__(REGS) mpc_step_kernel_r(const StepParams p) { mpc_step_body<T, WARPS>(p); }
 
 }  // namespace mpcb
