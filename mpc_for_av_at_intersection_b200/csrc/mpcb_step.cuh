@@ -463,27 +463,46 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
         double res_d = 1e300, res_p = 1e300, mu = 1e300;
         bool converged = false, broke = false;
         int it = 0;
-        for (; feasible0; ++it) {
-            double rda, rdd, rp[8];
-            {
+        // Residual bookkeeping.  A Newton step of length al scales BOTH linear residuals by (1 - al): r_p exactly (the
+        // slack step is defined from it), r_d up to the backward error of the LDL' solve.  The loop therefore carries
+        // the residuals forward by that factor and re-evaluates them from scratch (Hessian mat-vec, G and G' scans)
+        // only every fourth iteration and -- always -- before it accepts convergence or gives up, so the reported
+        // accuracy is that of freshly computed residuals.
+        double rda = 0.0, rdd = 0.0, rp[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) rp[c] = 0.0;
+        bool refresh = true, verified = false;
+        while (feasible0) {
+            if (refresh) {
                 double ga, gd, gta, gtd, g[8];
                 gradient(a, d, ga, gd);
                 GT_apply<T>(lam, dt, lane, gta, gtd);
                 rda = ga + gta; rdd = gd + gtd;
                 G_apply<T>(a, d, dt, lane, g);
-                double sl = 0.0, rpm = 0.0;
+                double rpm = 0.0;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     rp[c] = mk[c] ? g[c] + s[c] - hh8[c] : 0.0;
-                    sl += s[c] * lam[c];
                     rpm = fmax(rpm, fabs(rp[c]));
                 }
-                mu = warp_sum(sl) / m_cnt;
                 res_d = warp_max(fmax(fabs(rda), fabs(rdd)));
                 res_p = warp_max(rpm);
+                refresh = false; verified = true;
             }
-            if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) { converged = true; break; }
-            if (it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) break;
+            {
+                double sl = 0.0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) sl += s[c] * lam[c];
+                mu = warp_sum(sl) / m_cnt;
+            }
+            if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) {
+                if (verified) { converged = true; break; }
+                refresh = true; continue;
+            }
+            if (it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) {
+                if (verified) break;
+                refresh = true; continue;
+            }
 
             // ---- M = H + G' W G into registers (rows `lane` of A, B, C) ---------------------------------
             double sinv[8], w[8];
@@ -658,9 +677,14 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                 tmax = warp_max(tmax);
                 const double al = (tmax > 0.99) ? 0.99 / tmax : 1.0;
                 a += al * da; d += al * dd;
+                const double om = 1.0 - al;
 #pragma unroll
-                for (int c = 0; c < 8; ++c) { s[c] += al * dsa[c]; lam[c] += al * dla[c]; }
+                for (int c = 0; c < 8; ++c) { s[c] += al * dsa[c]; lam[c] += al * dla[c]; rp[c] *= om; }
+                rda *= om; rdd *= om; res_d *= om; res_p *= om;
             }
+            ++it;
+            verified = false;
+            refresh = (it & 3) == 0;
         }
         iters = it;
         if (converged) status = MPCB_ST_OPTIMAL;
