@@ -91,4 +91,12 @@ __device__ __forceinline__ double rcp(double x) {
 }
 __device__ __forceinline__ double clampd(double v, double lo, double hi) { return fmax(fmin(v, hi), lo); }
 
+// Predicated 16-byte shared store (one lane publishes {x, y}); a plain `if (lane == k) ...` with several
+// statements compiles to a divergent branch, an unconditional store by all lanes doubles the LSU wavefronts.
+__device__ __forceinline__ void sts_pair_if(bool pred, double* ptr, double x, double y) {
+    const unsigned addr = static_cast<unsigned>(__cvta_generic_to_shared(ptr));
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t@p st.shared.v2.f64 [%0], {%1, %2};\n\t}"
+                 :: "r"(addr), "d"(x), "d"(y), "r"((int)pred) : "memory");
+}
+
 }  // namespace mpcb

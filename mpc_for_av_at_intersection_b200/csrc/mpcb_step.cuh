@@ -56,8 +56,7 @@ struct WarpSmem {
     alignas(16) double LA[T * SA + 36];        // unscaled factor columns of the accel block (strictly lower, rest 0)
     alignas(16) double LB[T * SB + 36];        // cross block: column k (accel pivot k), rows = steer stages
     alignas(16) double LC[T * SA + 36];        // Schur complement (steer block), same layout as LA
-    double inv[N + 32];                        // 1 / d_k (+ one scratch slot per lane: branch-free publish)
-    double z[N + 32];                               // broadcast slot of the fused forward solve (already divided by d_k)
+    alignas(16) double2 iz[N];                 // {1 / d_k, broadcast slot of the fused forward solve (divided by d_k)}
     double bc[8][T + 1];                       // per-stage broadcast tables used while assembling H
     double tab[6][T];                          // per-stage model coefficients, re-read by the final prediction
 };
@@ -84,13 +83,13 @@ __device__ __forceinline__ void ldl_accel_steps(WarpSmem<T>& sm, double (&R)[T],
         // branch-free publish: idle lanes (>= T) write behind the column, into rows of column k + 1 that step k + 1
         // rewrites (or into the pad after the last column); lanes other than k write their own scratch slot
         sm.LA[col + lane] = a0s; sm.LB[SM::colB(k) + lane] = b0;
-        const int slot = mine ? k : SM::N + lane;
-        sm.inv[slot] = ivm; sm.z[slot] = ra * ivm;
+        sts_pair_if(mine, &sm.iz[k].x, ivm, ra * ivm);
         inva = mine ? ivm : inva;
         bad = bad || (mine && !(a0 > 0.0));
         __syncwarp();
         const double* pc = &sm.LA[col + k];
-        const double iv = sm.inv[k], zk = sm.z[k];
+        const double2 izk = sm.iz[k];
+        const double iv = izk.x, zk = izk.y;
         double c[JMAX + 2];
         c[1] = pc[1];
 #pragma unroll
@@ -121,13 +120,13 @@ __device__ __forceinline__ void ldl_steer_steps(WarpSmem<T>& sm, double (&C)[T],
         const int col = SM::colL(k);
         const double c0s = lane > k ? c0 : 0.0;
         sm.LC[col + lane] = c0s;
-        const int slot = mine ? T + k : SM::N + lane;
-        sm.inv[slot] = ivm; sm.z[slot] = rdl * ivm;
+        sts_pair_if(mine, &sm.iz[T + k].x, ivm, rdl * ivm);
         invd = mine ? ivm : invd;
         bad = bad || (mine && !(c0 > 0.0));
         __syncwarp();
         const double* pc = &sm.LC[col + k];
-        const double iv = sm.inv[T + k], zk = sm.z[T + k];
+        const double2 izk = sm.iz[T + k];
+        const double iv = izk.x, zk = izk.y;
         double c[JMAX + 2];
         c[1] = pc[1];
 #pragma unroll
@@ -557,7 +556,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
 #pragma unroll 1
                     for (int k = k0; k < k1; ++k) {
                         const double* col = &sm.LB[k * SM::SB + (ODD ? 1 : 0)];
-                        const double lb = col[lane] * sm.inv[k];
+                        const double lb = col[lane] * sm.iz[k].x;
                         if (ODD) C[0] -= lb * col[0];
 #pragma unroll
                         for (int j = ODD ? 1 : 0; j + 1 < T; j += 2) {
