@@ -153,6 +153,20 @@ def run_reference(args):
     return 0
 
 
+def ncu_traffic(B, T):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one step-kernel launch, from the committed ncu --set full
+    capture of the same configuration (profiles/*_step_traffic.json); None when no capture matches."""
+    import glob
+    for f in sorted(glob.glob(os.path.join(REPO, "profiles", "*_step_traffic.json")), reverse=True):
+        try:
+            d = json.load(open(f))
+            if d.get("batch") == B and d.get("horizon") == T:
+                return d["dram_bytes_read"] + d["dram_bytes_write"]
+        except Exception:
+            pass
+    return None
+
+
 def run_b200(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -281,8 +295,8 @@ def run_b200(args):
                     "api": "MpcSession.step -> mpcb_session_step_host (host buffers, pinned staging inside)"},
             "gpu_launches": launches,
             "roofline": {"bound": "fp64_fma", "achieved": ach_tflops, "peak": peak, "unit": "TFLOP/s",
-                         "frac": ach_tflops / peak if peak else None, "traffic": None,
-                         "kernel": f"mpcb::mpc_step_kernel<{T},4>", "flops_per_solve": F,
+                         "frac": ach_tflops / peak if peak else None, "traffic": ncu_traffic(B, T),
+                         "kernel": f"mpcb::mpc_step_kernel<{T},1,8> (one warp per problem, one warp per CTA, 8 CTAs/SM)", "flops_per_solve": F,
                          "peak_source": "measured live (mpcb_measure_fp64_peak: register-resident DFMA chains)",
                          "hbm": {"achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
                                  "peak_source": "MEASURED_PEAKS.json hbm_gbs" if os.path.exists(

@@ -17,7 +17,7 @@ KEYS = ["gpu__time_duration.sum", "launch__registers_per_thread", "launch__occup
         "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio",
-        "sm__icc_requests.sum", "sm__icc_requests_lookup_miss.sum", "sm__icc_requests_lookup_hit.sum"]
+        "sm__icc_requests.sum", "sm__icc_request_hit_rate.pct", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed", "sm__cycles_active.avg", "sm__cycles_elapsed.avg"]
 for rep in sys.argv[1:]:
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
