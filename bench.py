@@ -296,7 +296,8 @@ def run_b200(args):
             "gpu_launches": launches,
             "roofline": {"bound": "fp64_fma", "achieved": ach_tflops, "peak": peak, "unit": "TFLOP/s",
                          "frac": ach_tflops / peak if peak else None, "traffic": ncu_traffic(B, T),
-                         "kernel": f"mpcb::mpc_step_kernel<{T},1,8> (one warp per problem, one warp per CTA, 8 CTAs/SM)", "flops_per_solve": F,
+                         "kernel": (f"mpcb::mpc_step_kernel<{T},1,8> (one warp per problem, one warp per CTA, 8 CTAs/SM)" if T <= 31
+                                    else f"mpcb::mpc_step_long_kernel<128> (one CTA per problem, T={T})"), "flops_per_solve": F,
                          "peak_source": "measured live (mpcb_measure_fp64_peak: register-resident DFMA chains)",
                          "hbm": {"achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
                                  "peak_source": "MEASURED_PEAKS.json hbm_gbs" if os.path.exists(

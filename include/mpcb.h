@@ -90,7 +90,8 @@ int mpcb_device_count(void);
 int mpcb_create(const mpcb_config* cfg, int max_batch, int device, mpcb_handle** out);
 void mpcb_destroy(mpcb_handle* h);
 const char* mpcb_last_error(const mpcb_handle* h);   /* h may be NULL: last create error */
-/* horizons this build has kernels for; returns count, fills up to cap entries */
+/* horizons this build has kernels for (10, 13, 20: one warp per problem; 40, 80: one CTA per problem, the sizes of
+ * BASELINE.json configs[4]); returns count, fills up to cap entries */
 int mpcb_supported_horizons(int* out, int cap);
 
 /* replaces: smooth_yaw (main/lib/mpc.py:43-55).  Host, in place, returns yaw for chaining parity. */

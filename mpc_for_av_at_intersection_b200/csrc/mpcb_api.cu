@@ -8,6 +8,7 @@
 
 #include "../../include/mpcb.h"
 #include "mpcb_step.cuh"
+#include "mpcb_step_long.cuh"
 #include "mpcb_coupling.cuh"
 
 namespace {
@@ -121,7 +122,8 @@ __global__ void fp64_peak_kernel(double* out, int iters, double seed) {
 // ---------------------------------------------------------------------------------------------------
 namespace {
 
-constexpr int kHorizons[] = {10, 13, 20};
+constexpr int kHorizons[] = {10, 13, 20, 40, 80};      // <= 31: one warp per problem; longer: one CTA per problem
+constexpr int kLongThreads = 128;
 
 template <int T, int WARPS, int MINB>
 int launch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
@@ -159,6 +161,25 @@ int launch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
 }
 
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st);
+
+// long horizons (mpcb_step_long.cuh): one CTA of kLongThreads per problem, system matrix in shared memory
+int launch_step_long(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
+    const int T = h->cfg.T;
+    if (T + 1 > kLongThreads) { h->err = "mpcb: horizon too long for the CTA-per-problem kernel"; return MPCB_EINVAL; }
+    const size_t smem = mpcb::LongSmem::bytes(T, kLongThreads);
+    auto kern = mpcb::mpc_step_long_kernel<kLongThreads>;
+    static thread_local int configured_dev = -1;
+    static thread_local size_t configured_smem = 0;
+    if (configured_dev != h->device || configured_smem < smem) {
+        CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        configured_dev = h->device; configured_smem = smem;
+    }
+    kern<<<p.B, kLongThreads, smem, st>>>(p, T);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches++;
+    return MPCB_OK;
+}
 
 StepParams make_params(const mpcb_handle* h) {
     const mpcb_config& c = h->cfg;
@@ -445,6 +466,8 @@ int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
             }
 #endif
             return launch_step<20, 1, 8>(h, p, st);
+        case 40:
+        case 80: return launch_step_long(h, p, st);
         default: h->err = "mpcb: unsupported horizon"; return MPCB_EINVAL;
     }
 }

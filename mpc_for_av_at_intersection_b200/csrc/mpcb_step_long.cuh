@@ -1,0 +1,649 @@
+// mpcb_step_long.cuh -- the fused MPC step for LONG horizons (32 <= T <= NT - 1): one CTA per problem,
+// thread t <-> horizon stage t, the 2T x 2T system matrix resident in shared memory.
+//
+// Same reference rows as mpcb_step.cuh (A2..A8: main/lib/mpc.py:86-239,280-326, main/lib/trajectories.py:100-126,
+// main/lib/simulation.py:35-47), same condensed model and the same Mehrotra interior point; what changes is the
+// execution shape.  BASELINE.json configs[4] sweeps T in {10, 13, 20, 40, 80}: at T = 80 the condensed system has
+// n = 160 unknowns, its packed lower triangle is 103 KB -- it cannot live in the registers of one warp, so
+//   * every warp-level primitive of the short kernel (scan, neighbour shift, broadcast, reduction) becomes a
+//     block-level one (two-level: shuffles inside the warps, one shared-memory pass across them);
+//   * M = H + G'WG is assembled every iteration from the per-stage moment tables (H is never stored: an entry is
+//     ~10 FMAs from tables that are resident anyway) and factorised in place (right-looking LDL', warps take rows,
+//     lanes take columns: conflict-free row-major packed storage);
+//   * the gradient is evaluated by the forward/adjoint scans (O(T) per iteration) instead of a Hessian mat-vec.
+// This is the throughput-insensitive end of the sweep (n^3 work per iteration): it is built for parity and coverage.
+#pragma once
+#include "mpcb_common.cuh"
+#include "mpcb_step.cuh"
+
+namespace mpcb {
+
+template <int NT>
+struct BlockOps {
+    static constexpr int NW = NT / 32;
+    double* red;      // NW + 2 doubles of scratch
+    int* redi;        // NW + 2 ints of scratch
+    int tid, lane, wid;
+    __device__ __forceinline__ BlockOps(double* r, int* ri) : red(r), redi(ri), tid(threadIdx.x), lane(threadIdx.x & 31), wid(threadIdx.x >> 5) {}
+    // inclusive prefix sum over threads 0..tid
+    __device__ __forceinline__ double scan_up(double v) {
+        v = mpcb::scan_up(v, lane);
+        if (lane == 31) red[wid] = v;
+        __syncthreads();
+        double off = 0.0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) off += (w < wid) ? red[w] : 0.0;
+        __syncthreads();
+        return v + off;
+    }
+    // inclusive suffix sum over threads tid..NT-1
+    __device__ __forceinline__ double scan_dn(double v) {
+        v = mpcb::scan_dn(v, lane);
+        if (lane == 0) red[wid] = v;
+        __syncthreads();
+        double off = 0.0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) off += (w > wid) ? red[w] : 0.0;
+        __syncthreads();
+        return v + off;
+    }
+    __device__ __forceinline__ double sum(double v) {
+        v = warp_sum(v);
+        if (lane == 0) red[wid] = v;
+        __syncthreads();
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) s += red[w];
+        __syncthreads();
+        return s;
+    }
+    __device__ __forceinline__ double max(double v) {
+        v = warp_max(v);
+        if (lane == 0) red[wid] = v;
+        __syncthreads();
+        double s = red[0];
+#pragma unroll
+        for (int w = 1; w < NW; ++w) s = fmax(s, red[w]);
+        __syncthreads();
+        return s;
+    }
+    // value of thread tid+1 (0 past the end) / tid-1 (0 before the start)
+    __device__ __forceinline__ double dn1(double v) {
+        double n = __shfl_down_sync(MPCB_FULL, v, 1);
+        if (lane == 0) red[wid] = v;
+        __syncthreads();
+        if (lane == 31) n = (wid + 1 < NW) ? red[wid + 1] : 0.0;
+        __syncthreads();
+        return n;
+    }
+    __device__ __forceinline__ double up1(double v) {
+        double n = __shfl_up_sync(MPCB_FULL, v, 1);
+        if (lane == 31) red[wid] = v;
+        __syncthreads();
+        if (lane == 0) n = (wid > 0) ? red[wid - 1] : 0.0;
+        __syncthreads();
+        return n;
+    }
+    __device__ __forceinline__ int dn1i(int v) {
+        int n = __shfl_down_sync(MPCB_FULL, v, 1);
+        if (lane == 0) redi[wid] = v;
+        __syncthreads();
+        if (lane == 31) n = (wid + 1 < NW) ? redi[wid + 1] : 0;
+        __syncthreads();
+        return n;
+    }
+    // block arg-min on (distance, index), ties to the lower index; every thread gets the winner's index
+    __device__ __forceinline__ int argmin(double d, int i) {
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            const double d2 = __shfl_xor_sync(MPCB_FULL, d, o);
+            const int i2 = __shfl_xor_sync(MPCB_FULL, i, o);
+            if (d2 < d || (d2 == d && i2 < i)) { d = d2; i = i2; }
+        }
+        if (lane == 0) { red[wid] = d; redi[wid] = i; }
+        __syncthreads();
+        d = red[0]; i = redi[0];
+#pragma unroll
+        for (int w = 1; w < NW; ++w) {
+            const double d2 = red[w];
+            const int i2 = redi[w];
+            if (d2 < d || (d2 == d && i2 < i)) { d = d2; i = i2; }
+        }
+        __syncthreads();
+        return i;
+    }
+};
+
+// main/lib/trajectories.py:100-126, forward=True, block version of nearest_index_in_direction
+template <int NT>
+__device__ __forceinline__ int nearest_index_block(BlockOps<NT>& bo, const double* __restrict__ cx,
+                                                   const double* __restrict__ cy, int start, int nc, double x, double y) {
+    const int n = nc - start;
+    if (n <= 1) return start;
+    if (n == 2) return start + 1;
+    double bd[3] = {1e300, 1e300, 1e300};
+    int bi[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
+    for (int j = start + bo.tid; j < nc; j += NT) {
+        const double dx = __dsub_rn(cx[j], x), dy = __dsub_rn(cy[j], y);
+        const double d = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+        top3_insert(d, j, bd, bi);
+    }
+    int ind[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const int i = bo.argmin(bd[0], bi[0]);
+        ind[r] = i;
+        if (bi[0] == i) {
+            bd[0] = bd[1]; bi[0] = bi[1];
+            bd[1] = bd[2]; bi[1] = bi[2];
+            bd[2] = 1e300; bi[2] = 0x7fffffff;
+        }
+    }
+    if (abs(ind[1] - ind[2]) == 2) return ind[0];
+    if (abs(ind[0] - ind[1]) == 1) return max(ind[0], ind[1]);
+    return -1;
+}
+
+// shared-memory carve-up of one problem (doubles): M packed lower row-major, then the per-stage tables
+struct LongSmem {
+    int T, n;
+    double* M;        // n (n + 1) / 2
+    double* vec;      // n      right-hand side / solution
+    double* dinv;     // n
+    double* colb;     // n      unscaled pivot column
+    double* tab;      // NTAB x (T + 1) per-stage tables
+    double* red;      // scratch of the block primitives
+    int* redi;
+    static constexpr int NTAB = 24;
+    __host__ __device__ static size_t bytes(int T, int NT) {
+        const size_t n = 2 * (size_t)T;
+        return (n * (n + 1) / 2 + 3 * n + (size_t)NTAB * (T + 1) + NT / 32 + 4) * sizeof(double) + (NT / 32 + 4) * sizeof(int);
+    }
+    __device__ __forceinline__ void carve(unsigned char* raw, int T_, int NT) {
+        T = T_; n = 2 * T_;
+        double* q = reinterpret_cast<double*>(raw);
+        M = q; q += (size_t)n * (n + 1) / 2;
+        vec = q; q += n;
+        dinv = q; q += n;
+        colb = q; q += n;
+        tab = q; q += (size_t)NTAB * (T + 1);
+        red = q; q += NT / 32 + 4;
+        redi = reinterpret_cast<int*>(q);
+    }
+    __device__ __forceinline__ double* t(int i) const { return tab + (size_t)i * (T + 1); }
+};
+
+
+// table slots
+enum { LT_OA = 0, LT_TERM, LT_ZX, LT_ZY, LT_WX, LT_WY, LT_BB, LT_HH, LT_GAX, LT_GAY, LT_GCX, LT_GCY, LT_HA, LT_HC, LT_HB,
+       LT_DGA, LT_DGC, LT_WVS, LT_DA, LT_DC, LT_WRP, LT_U0, LT_U1, LT_SPARE };
+
+template <int NT>
+__global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, const int T) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int b = blockIdx.x;
+    if (b >= p.B) return;
+    LongSmem sm;
+    sm.carve(smem_raw, T, NT);
+    BlockOps<NT> bo(sm.red, sm.redi);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    constexpr int NW = NT / 32;
+    const bool act = tid < T;
+    const double dt = p.dt;
+    const int n = 2 * T;
+
+    if (p.done && p.done[b] != 0) return;
+    const double x0 = p.state[4 * b + 0], y0 = p.state[4 * b + 1], yaw0 = p.state[4 * b + 2], v0 = p.state[4 * b + 3];
+    const int route = p.route[b];
+    const int nc = p.ncourse[b];
+    if (p.fuse_goal) {       // MPC.is_goal (main/lib/mpc.py:310-326)
+        const double gd = hypot(x0 - p.goal[2 * b], y0 - p.goal[2 * b + 1]);
+        const bool isgoal = gd <= p.goal_dis && abs(p.target_ind[b] - nc) < 5 && fabs(v0) <= p.stop_speed;
+        if (isgoal) { __syncthreads(); if (tid == 0) p.done[b] = 1; return; }
+    }
+    const double L = p.L ? p.L[b] : p.wheelbase;
+    const double dl = p.dl[route];
+    const double* __restrict__ cx = p.courses + (size_t)route * 3 * p.ncmax;
+    const double* __restrict__ cy = cx + p.ncmax;
+    const double* __restrict__ cyaw = cy + p.ncmax;
+    int tind = p.target_ind[b];
+    const int warm = p.warm[b];
+    double oa = (warm && act) ? p.oa[(size_t)b * T + tid] : 0.0;     // mpc.py:222-224
+    double od = (warm && act) ? p.od[(size_t)b * T + tid] : 0.0;
+
+    int status = MPCB_ST_OPTIMAL, iters = 0;
+    bool solved = false, have_ov = false;
+    double sx = 0.0, sy = 0.0, sv = 0.0, sph = 0.0;    // solution states at index tid (0..T)
+    double xr_x = 0.0, xr_y = 0.0, xr_yaw = 0.0;       // xref at state index tid (0..T)
+    auto idx = [](int i, int j) { return i * (i + 1) / 2 + j; };
+
+    for (int pass = 0; pass < p.max_iter; ++pass) {
+        // ---- A2: reference lookup (main/lib/mpc.py:86-109) ------------------------------------------------
+        const int ni = nearest_index_block<NT>(bo, cx, cy, tind, nc, x0, y0);
+        if (ni < 0) { status = MPCB_ST_NEAREST; break; }
+        tind = ni;
+        double trav = 0.0;
+        if (!have_ov) {
+            const double pstep = __dmul_rn(fabs(fmax(v0, p.min_ref_speed)), dt);
+            double acc = 0.0;
+            for (int i = 0; i <= T; ++i) {
+                acc = (i == 0) ? pstep : __dadd_rn(acc, pstep);                     // np.cumsum is sequential
+                if (i == tid) trav = acc;
+            }
+        } else {
+            if (tid <= T) sm.t(LT_TERM)[tid] = __dmul_rn(fabs(sv), dt);
+            __syncthreads();
+            double acc = 0.0;
+            for (int i = 0; i <= T; ++i) {
+                const double ti = sm.t(LT_TERM)[i];
+                acc = (i == 0) ? ti : __dadd_rn(acc, ti);
+                if (i == tid) trav = acc;
+            }
+            __syncthreads();
+        }
+        int ix = (int)rint(__ddiv_rn(trav, dl)) + tind;    // np.rint: half to even
+        ix = min(ix, nc - 1);
+        if (tid > T) ix = nc - 1;
+        ix = max(ix, 0);
+        xr_x = cx[ix]; xr_y = cy[ix]; xr_yaw = cyaw[ix];
+        const bool reach = (ix == nc - 1);
+
+        // ---- A3: rollout of the previous (unshifted) solution (main/lib/mpc.py:112-126) ---------------------
+        const double dcl = clampd(od, -p.max_steer, p.max_steer);
+        const double tnd = act ? tan(dcl) : 0.0;
+        if (act) sm.t(LT_OA)[tid] = oa;
+        __syncthreads();
+        double vb = v0, vcur = v0;
+        for (int t = 0; t < T - 1; ++t) {
+            vcur = clampd(__dadd_rn(vcur, __dmul_rn(sm.t(LT_OA)[t], dt)), p.min_speed, p.max_speed);
+            if (tid == t + 1) vb = vcur;
+        }
+        const double yterm = __dmul_rn(__dmul_rn(__ddiv_rn(vb, L), tnd), dt);
+        if (act) sm.t(LT_TERM)[tid] = yterm;
+        __syncthreads();
+        double pb = yaw0, pcur = yaw0;
+        for (int t = 0; t < T - 1; ++t) {
+            pcur = __dadd_rn(pcur, sm.t(LT_TERM)[t]);
+            if (tid == t + 1) pb = pcur;
+        }
+        __syncthreads();
+
+        // ---- A4: linearisation coefficients of stage tid (main/lib/mpc.py:58-79, steer operating point 0) --
+        double sn, cs;
+        sincos(pb, &sn, &cs);
+        const double dtv = dt * vb;
+        const double c_ = act ? dt * cs : 0.0, s_ = act ? dt * sn : 0.0;
+        const double pp = act ? dtv * sn : 0.0, qq = act ? dtv * cs : 0.0;
+        const double bb = act ? dtv / L : 0.0;
+        if (!act) pb = 0.0;
+        const double cn = bo.dn1(c_), snn = bo.dn1(s_), ppn = bo.dn1(pp), qqn = bo.dn1(qq);
+
+        // ---- A5: stage weights for state tid+1, input weights for stage tid (main/lib/mpc.py:151-184) ------
+        const double rx = bo.dn1(xr_x), ry = bo.dn1(xr_y), rpsi = bo.dn1(xr_yaw);
+        const bool reach_n = bo.dn1i((int)reach) != 0;
+        double m11 = 0.0, m12 = 0.0, m22 = 0.0, wv = 0.0, wp = 0.0;
+        if (act) {
+            if (!reach_n) {
+                double s1, c1, s2, c2;
+                sincos(rpsi + 0.5 * 3.141592653589793, &s1, &c1);
+                sincos(rpsi, &s2, &c2);
+                m11 = p.w_perp * (c1 * c1) + p.w_para * (c2 * c2);
+                m12 = p.w_perp * (c1 * s1) + p.w_para * (c2 * s2);
+                m22 = p.w_perp * (s1 * s1) + p.w_para * (s2 * s2);
+                wv = p.Qv; wp = p.Qyaw;
+            } else { m11 = p.Qf0; m22 = p.Qf1; wv = p.Qf2; wp = p.Qf3; }
+        }
+        const double ra_w = act ? (reach ? p.r_end : p.R0) : 0.0;
+        const double rd_w = act ? (reach ? p.r_end : p.R1) : 0.0;
+
+        // ---- per-stage moment tables of the condensed Hessian ------------------------------------------------
+        const double Zx = bo.scan_up(c_), Zy = bo.scan_up(s_);
+        const double Wx = bo.scan_up(-pp), Wy = bo.scan_up(qq);
+        {
+            const double MZx = m11 * Zx + m12 * Zy, MZy = m12 * Zx + m22 * Zy;
+            const double MWx = m11 * Wx + m12 * Wy, MWy = m12 * Wx + m22 * Wy;
+            const double S11 = bo.scan_dn(m11), S12 = bo.scan_dn(m12), S22 = bo.scan_dn(m22);
+            const double S1zx = bo.scan_dn(MZx), S1zy = bo.scan_dn(MZy);
+            const double S1wx = bo.scan_dn(MWx), S1wy = bo.scan_dn(MWy);
+            const double S2zz = bo.scan_dn(Zx * MZx + Zy * MZy);
+            const double S2ww = bo.scan_dn(Wx * MWx + Wy * MWy);
+            const double S2wz = bo.scan_dn(Wx * MZx + Wy * MZy);
+            const double Sv = bo.scan_dn(wv), Sp = bo.scan_dn(wp);
+            const double gAx = S11 * Zx + S12 * Zy - S1zx, gAy = S12 * Zx + S22 * Zy - S1zy;
+            const double gCx = S11 * Wx + S12 * Wy - S1wx, gCy = S12 * Wx + S22 * Wy - S1wy;
+            const double hA = S2zz - (Zx * S1zx + Zy * S1zy) + Sv;
+            const double hC = S2ww - (Wx * S1wx + Wy * S1wy) + Sp;
+            const double hB = S2wz - (Wx * S1zx + Wy * S1zy);
+            const double hh = S2wz - (Zx * S1wx + Zy * S1wy);
+            const int nb = (tid > 0 ? 1 : 0) + (tid < T - 1 ? 1 : 0);
+            if (act) {
+                sm.t(LT_ZX)[tid] = Zx; sm.t(LT_ZY)[tid] = Zy; sm.t(LT_WX)[tid] = Wx; sm.t(LT_WY)[tid] = Wy;
+                sm.t(LT_BB)[tid] = bb; sm.t(LT_HH)[tid] = hh;
+                sm.t(LT_GAX)[tid] = gAx; sm.t(LT_GAY)[tid] = gAy; sm.t(LT_GCX)[tid] = gCx; sm.t(LT_GCY)[tid] = gCy;
+                sm.t(LT_HA)[tid] = hA; sm.t(LT_HC)[tid] = hC; sm.t(LT_HB)[tid] = hB;
+                sm.t(LT_DGA)[tid] = 2.0 * ra_w + 2.0 * p.Rd0 * nb; sm.t(LT_DGC)[tid] = 2.0 * rd_w + 2.0 * p.Rd1 * nb;
+            }
+            __syncthreads();
+        }
+
+        // ---- linear prediction and objective gradient by scans (oracle/condensed_model.py states()/grad()) ----
+        auto predict = [&](double a, double d, double& xs, double& ys, double& vs, double& phs) {
+            const double sa = bo.scan_up(a);
+            const double bd_ = bb * d;
+            const double sp_ = bo.scan_up(bd_);
+            vs = v0 + dt * sa;
+            phs = yaw0 + sp_;
+            const double vt = v0 + dt * (sa - a);
+            const double dph = (yaw0 + (sp_ - bd_)) - pb;
+            xs = x0 + bo.scan_up(c_ * vt - pp * dph);
+            ys = y0 + bo.scan_up(s_ * vt + qq * dph);
+        };
+        auto gradient = [&](double a, double d, double& ga, double& gd) {
+            double xs, ys, vs, phs;
+            predict(a, d, xs, ys, vs, phs);
+            const double ex = xs - rx, ey = ys - ry;
+            const double lx = 2.0 * (m11 * ex + m12 * ey), ly = 2.0 * (m12 * ex + m22 * ey);
+            const double lv = 2.0 * wv * vs, lp = 2.0 * wp * (phs - rpsi);      // xref[2,:] = 0 (mpc.py:102-105)
+            const double px = bo.scan_dn(act ? lx : 0.0), py = bo.scan_dn(act ? ly : 0.0);
+            const double pxn = bo.dn1(px), pyn = bo.dn1(py);
+            const double pv = bo.scan_dn(act ? lv + cn * pxn + snn * pyn : 0.0);
+            const double pph = bo.scan_dn(act ? lp - ppn * pxn + qqn * pyn : 0.0);
+            const double ap = bo.up1(a), an = bo.dn1(a);
+            const double dp = bo.up1(d), dn = bo.dn1(d);
+            const double fa = (tid > 0 ? a - ap : 0.0) - (tid < T - 1 ? an - a : 0.0);
+            const double fd = (tid > 0 ? d - dp : 0.0) - (tid < T - 1 ? dn - d : 0.0);
+            ga = act ? dt * pv + 2.0 * ra_w * a + 2.0 * p.Rd0 * fa : 0.0;
+            gd = act ? bb * pph + 2.0 * rd_w * d + 2.0 * p.Rd1 * fd : 0.0;
+        };
+        // structured constraint operator, slots as in mpcb_step.cuh (main/lib/mpc.py:184,187-191)
+        auto G_apply = [&](double a, double d, double (&g)[8]) {
+            const double dn = bo.dn1(d);
+            const double dd = (tid < T - 1) ? dn - d : 0.0;
+            const double cs2 = dt * bo.scan_up(a);
+            g[0] = a; g[1] = -a; g[2] = d; g[3] = -d; g[4] = dd; g[5] = -dd; g[6] = cs2; g[7] = -cs2;
+        };
+        auto GT_apply = [&](const double (&y)[8], double& ga, double& gd) {
+            ga = y[0] - y[1] + dt * bo.scan_dn(y[6] - y[7]);
+            const double r = y[4] - y[5];
+            gd = y[2] - y[3] - r + bo.up1(r);
+        };
+
+        // ---- A6: interior point on  min J(u)  s.t.  G u <= h -------------------------------------------------
+        double hh8[8];
+        hh8[0] = p.max_accel; hh8[1] = -p.max_decel; hh8[2] = p.max_steer; hh8[3] = p.max_steer;
+        hh8[4] = p.dsteer_dt; hh8[5] = p.dsteer_dt; hh8[6] = p.max_speed - v0; hh8[7] = v0 - p.min_speed;
+        bool mk[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) mk[c] = (c == 4 || c == 5) ? (tid < T - 1) : act;
+        const double m_cnt = 8.0 * T - 2.0;
+        const bool feasible0 = (hh8[6] >= -1e-9) && (hh8[7] >= -1e-9);
+
+        double a = act ? oa : 0.0, d = act ? od : 0.0;
+        double s[8], lam[8];
+        {
+            double g[8];
+            G_apply(a, d, g);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                s[c] = mk[c] ? fmax(hh8[c] - g[c], 1.0) : 1.0;
+                lam[c] = mk[c] ? 1.0 : 0.0;
+            }
+        }
+        double gscale;
+        {
+            double g0a, g0d;
+            gradient(0.0, 0.0, g0a, g0d);
+            gscale = 1.0 + bo.max(fmax(fabs(g0a), fabs(g0d)));
+        }
+        double res_d = 1e300, res_p = 1e300, mu = 1e300;
+        bool converged = false;
+        int it = 0;
+        while (feasible0) {
+            double rda, rdd, rp[8];
+            {
+                double ga, gd, gta, gtd, g[8];
+                gradient(a, d, ga, gd);
+                GT_apply(lam, gta, gtd);
+                rda = ga + gta; rdd = gd + gtd;
+                G_apply(a, d, g);
+                double sl = 0.0, rpm = 0.0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    rp[c] = mk[c] ? g[c] + s[c] - hh8[c] : 0.0;
+                    sl += s[c] * lam[c];
+                    rpm = fmax(rpm, fabs(rp[c]));
+                }
+                mu = bo.sum(sl) / m_cnt;
+                res_d = bo.max(fmax(fabs(rda), fabs(rdd)));
+                res_p = bo.max(rpm);
+            }
+            if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) { converged = true; break; }
+            if (it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) break;
+
+            double sinv[8], w[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) { sinv[c] = rcp(s[c]); w[c] = lam[c] * sinv[c]; }
+            {
+                const double wv_suf = dt * dt * bo.scan_dn(w[6] + w[7]);
+                const double wr = w[4] + w[5];
+                const double wr_prev = bo.up1(wr);
+                if (act) {
+                    sm.t(LT_WVS)[tid] = wv_suf; sm.t(LT_DA)[tid] = w[0] + w[1];
+                    sm.t(LT_DC)[tid] = w[2] + w[3] + wr + wr_prev; sm.t(LT_WRP)[tid] = wr_prev;
+                }
+            }
+            // affine right-hand side: -r_d + G'(lam - W r_p)
+            {
+                double y[8], ya, yd;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) y[c] = lam[c] - w[c] * rp[c];
+                GT_apply(y, ya, yd);
+                if (act) { sm.vec[tid] = ya - rda; sm.vec[T + tid] = yd - rdd; }
+            }
+            __syncthreads();
+            // ---- assemble M = H + G'WG (packed lower, row-major; unknowns a_0..a_{T-1}, d_0..d_{T-1}) ---------
+            {
+                const double kA = 2.0 * dt * dt;
+                for (int i = wid; i < n; i += NW) {
+                    double* row = sm.M + idx(i, 0);
+                    if (i < T) {                                   // accel row i, accel columns j <= i
+                        const double hA = sm.t(LT_HA)[i], gAx = sm.t(LT_GAX)[i], gAy = sm.t(LT_GAY)[i], wvs = sm.t(LT_WVS)[i];
+                        for (int j = lane; j <= i; j += 32) {
+                            double v = kA * (hA + sm.t(LT_ZX)[j] * gAx + sm.t(LT_ZY)[j] * gAy) + wvs;
+                            if (j == i) v += sm.t(LT_DGA)[i] + sm.t(LT_DA)[i];
+                            if (j == i - 1) v -= 2.0 * p.Rd0;
+                            row[j] = v;
+                        }
+                    } else {                                       // steer row r = i - T
+                        const int r = i - T;
+                        const double bbr = sm.t(LT_BB)[r], kB = 2.0 * bbr * dt, kC = 2.0 * bbr;
+                        const double hB = sm.t(LT_HB)[r], hC = sm.t(LT_HC)[r], gCx = sm.t(LT_GCX)[r], gCy = sm.t(LT_GCY)[r];
+                        const double Wxr = sm.t(LT_WX)[r], Wyr = sm.t(LT_WY)[r];
+                        for (int j = lane; j < T; j += 32) {       // cross block: accel column j
+                            const double Blo = hB + sm.t(LT_ZX)[j] * gCx + sm.t(LT_ZY)[j] * gCy;
+                            const double Bup = sm.t(LT_HH)[j] + Wxr * sm.t(LT_GAX)[j] + Wyr * sm.t(LT_GAY)[j];
+                            row[j] = kB * ((j <= r) ? Blo : Bup);
+                        }
+                        for (int j = lane; j <= r; j += 32) {      // steer block: steer column j <= r
+                            double v = kC * sm.t(LT_BB)[j] * (hC + sm.t(LT_WX)[j] * gCx + sm.t(LT_WY)[j] * gCy);
+                            if (j == r) v += sm.t(LT_DGC)[r] + sm.t(LT_DC)[r];
+                            if (j == r - 1) v -= 2.0 * p.Rd1 + sm.t(LT_WRP)[r];
+                            row[T + j] = v;
+                        }
+                    }
+                }
+            }
+            // ---- LDL' in place (right-looking): column k is scaled, the trailing rows go to the warps -----------
+            bool bad = false;
+            for (int k = 0; k < n; ++k) {
+                __syncthreads();
+                const double dk = sm.M[idx(k, k)];
+                bad = bad || !(dk > 0.0);
+                const double iv = rcp(dk);
+                for (int i = k + 1 + tid; i < n; i += NT) {
+                    const double v = sm.M[idx(i, k)];
+                    sm.colb[i] = v;
+                    sm.M[idx(i, k)] = v * iv;
+                }
+                if (tid == 0) sm.dinv[k] = iv;
+                __syncthreads();
+                for (int i = k + 1 + wid; i < n; i += NW) {
+                    const double li = sm.colb[i] * iv;
+                    double* row = sm.M + idx(i, 0);
+                    for (int j = k + 1 + lane; j <= i; j += 32) row[j] = fma(-li, sm.colb[j], row[j]);
+                }
+            }
+            __syncthreads();
+            if (bad) break;
+            // L D L' x = vec, in place
+            auto solve = [&]() {
+                for (int k = 0; k < n - 1; ++k) {                  // forward, column oriented
+                    const double yk = sm.vec[k];
+                    for (int i = k + 1 + tid; i < n; i += NT) sm.vec[i] = fma(-sm.M[idx(i, k)], yk, sm.vec[i]);
+                    __syncthreads();
+                }
+                for (int i = tid; i < n; i += NT) sm.vec[i] *= sm.dinv[i];
+                __syncthreads();
+                for (int k = n - 1; k >= 1; --k) {                 // backward: row k of L is contiguous
+                    const double xk = sm.vec[k];
+                    const double* row = sm.M + idx(k, 0);
+                    for (int j = tid; j < k; j += NT) sm.vec[j] = fma(-row[j], xk, sm.vec[j]);
+                    __syncthreads();
+                }
+            };
+
+            // ---- predictor ---------------------------------------------------------------------------------------
+            double dsa[8], dla[8];
+            double sigma_mu;
+            {
+                solve();
+                const double da = act ? sm.vec[tid] : 0.0, dd = act ? sm.vec[T + tid] : 0.0;
+                double g[8];
+                G_apply(da, dd, g);
+                double tmax = 0.0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
+                    dla[c] = mk[c] ? -lam[c] - w[c] * dsa[c] : 0.0;
+                    const double linv = mk[c] ? rcp(lam[c]) : 0.0;
+                    tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
+                }
+                tmax = bo.max(tmax);
+                const double al = 1.0 / fmax(1.0, tmax);
+                double sl = 0.0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) sl += (s[c] + al * dsa[c]) * (lam[c] + al * dla[c]);
+                const double mu_aff = bo.sum(sl) / m_cnt;
+                const double r = mu_aff / mu;
+                sigma_mu = r * r * r * mu;
+            }
+            // ---- corrector ---------------------------------------------------------------------------------------
+            {
+                double rc[8], y[8], ya, yd;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    rc[c] = mk[c] ? s[c] * lam[c] + dsa[c] * dla[c] - sigma_mu : 0.0;
+                    y[c] = rc[c] * sinv[c] - w[c] * rp[c];
+                }
+                GT_apply(y, ya, yd);
+                if (act) { sm.vec[tid] = ya - rda; sm.vec[T + tid] = yd - rdd; }
+                __syncthreads();
+                solve();
+                const double da = act ? sm.vec[tid] : 0.0, dd = act ? sm.vec[T + tid] : 0.0;
+                double g[8];
+                G_apply(da, dd, g);
+                double tmax = 0.0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
+                    dla[c] = mk[c] ? -(rc[c] + lam[c] * dsa[c]) * sinv[c] : 0.0;
+                    const double linv = mk[c] ? rcp(lam[c]) : 0.0;
+                    tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
+                }
+                tmax = bo.max(tmax);
+                const double al = (tmax > 0.99) ? 0.99 / tmax : 1.0;
+                a += al * da; d += al * dd;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) { s[c] += al * dsa[c]; lam[c] += al * dla[c]; }
+            }
+            ++it;
+        }
+        iters = it;
+        if (converged) status = MPCB_ST_OPTIMAL;
+        else if (feasible0 && res_d < 1e-6 * gscale && res_p < 1e-7 && mu < 1e-7) status = MPCB_ST_INACCURATE;
+        else { status = MPCB_ST_FAILED; solved = false; break; }
+        solved = true;
+        oa = a; od = d;
+        {
+            double xs, ys, vs, phs;
+            predict(a, d, xs, ys, vs, phs);
+            sx = bo.up1(xs); sy = bo.up1(ys); sv = bo.up1(vs); sph = bo.up1(phs);    // thread t holds state t
+            if (tid == 0) { sx = x0; sy = y0; sv = v0; sph = yaw0; }
+        }
+        have_ov = true;
+    }
+
+    // ---- A7: bookkeeping of MPC.step (main/lib/mpc.py:289-299) -------------------------------------------------
+    if (status == MPCB_ST_NEAREST) {
+        if (tid == 0) { p.status[b] = status; if (p.iters) p.iters[b] = 0; if (p.fuse_plant && p.done) p.done[b] = 2; }
+        return;
+    }
+    const size_t tb = (size_t)b * 4 * (T + 1);
+    if (p.xref && tid <= T) {
+        p.xref[tb + tid] = xr_x;
+        p.xref[tb + (T + 1) + tid] = xr_y;
+        p.xref[tb + 2 * (T + 1) + tid] = 0.0;
+        p.xref[tb + 3 * (T + 1) + tid] = xr_yaw;
+    }
+    const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+    if (solved) {
+        if (act) { p.oa[(size_t)b * T + tid] = oa; p.od[(size_t)b * T + tid] = od; }
+        if (p.traj && tid <= T) {
+            p.traj[tb + tid] = sx;
+            p.traj[tb + (T + 1) + tid] = sy;
+            p.traj[tb + 2 * (T + 1) + tid] = sv;
+            p.traj[tb + 3 * (T + 1) + tid] = sph;
+        }
+    } else if (p.traj && tid <= T) {
+        for (int r = 0; r < 4; ++r) p.traj[tb + r * (T + 1) + tid] = qnan;
+    }
+    // applied controls: first stage of the solution, else the reference's fallback (mpc.py:294-297)
+    if (tid == 0) { sm.vec[0] = od; sm.vec[1] = oa; }
+    __syncthreads();
+    const double di = solved ? sm.vec[0] : p.di_ai[2 * b];
+    const double ai = solved ? sm.vec[1] : p.max_decel;
+    double dev = qnan;
+    if (solved && tind < nc) {      // get_current_xref_deviation (mpc.py:301-308)
+        const double ang = cyaw[tind] + 3.141592653589793 / 2;
+        const double ex = cos(ang) * (cx[tind] - x0), ey = sin(ang) * (cy[tind] - y0);
+        dev = sqrt(ex * ex + ey * ey);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        p.target_ind[b] = tind;
+        p.status[b] = status;
+        if (p.iters) p.iters[b] = iters;
+        p.warm[b] = solved ? 1 : 0;
+        if (solved) { p.di_ai[2 * b] = di; p.di_ai[2 * b + 1] = ai; }
+        else p.di_ai[2 * b + 1] = p.max_decel;
+        if (p.xdev) p.xdev[b] = dev;
+    }
+    if (p.fuse_plant) {      // Simulation.step (main/lib/simulation.py:35-47, main/bicycle/main.py:28-41)
+        const double dcl = clampd(di, -p.max_steer, p.max_steer);
+        double sn, cs;
+        sincos(yaw0, &sn, &cs);
+        const double xd = __dmul_rn(v0, cs), yd = __dmul_rn(v0, sn);
+        const double td = __dmul_rn(__ddiv_rn(v0, L), tan(dcl));
+        const double nx = __dadd_rn(x0, __dmul_rn(xd, dt)), ny = __dadd_rn(y0, __dmul_rn(yd, dt));
+        const double nyaw = __dadd_rn(yaw0, __dmul_rn(td, dt));
+        const double nv = clampd(__dadd_rn(v0, __dmul_rn(ai, dt)), p.min_speed, p.max_speed);
+        double col = nx;
+        col = tid == 1 ? ny : col;  col = tid == 2 ? nyaw : col;  col = tid == 3 ? nv : col;
+        col = tid == 4 ? di : col;  col = tid == 5 ? ai : col;    col = tid == 6 ? dev : col;
+        col = tid == 7 ? (double)status : col;
+        if (tid < 4) p.state_out[4 * b + tid] = col;
+        if (p.history && tid < 8) p.history[8 * (size_t)b + tid] = col;
+    }
+}
+
+}  // namespace mpcb

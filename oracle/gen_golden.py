@@ -81,7 +81,7 @@ def record_step(rec, mpc, state, route_id, loop_id, step, extra=None):
     return di, ai, raised
 
 
-def closed_loops(T, routes_raw):
+def closed_loops(T, routes_raw, cases=None, max_steps=400):
     cfg = rh.setup({"T": T})
     mpcmod = rh.load_mpc()
     from lib.car_dimensions import BicycleModelDimensions
@@ -93,7 +93,8 @@ def closed_loops(T, routes_raw):
 
     car = BicycleModelDimensions(skip_back_circle_collision_checking=False)
     rec = Recorder(T)
-    cases = [(rid, False) for rid in range(len(ROUTES))] + [(ROUTES.index((4, 1)), True)]
+    if cases is None:
+        cases = [(rid, False) for rid in range(len(ROUTES))] + [(ROUTES.index((4, 1)), True)]
     loop_len = []
     for loop_id, (rid, with_obs) in enumerate(cases):
         trajectory_full = routes_raw[rid].copy()
@@ -111,7 +112,7 @@ def closed_loops(T, routes_raw):
         EXTRA = 4 * int(math.ceil(car.radius / dl))
         traj_agent_idx = 0
         tmp_trajectory = None
-        for i in range(400):
+        for i in range(max_steps):
             if mpc.is_goal(state):
                 break
             # mpc_intersection.py:103-139
@@ -233,5 +234,21 @@ def main():
         random_problems(T, routes_raw, n=400, seed=1000 + T)
 
 
+def main_long():
+    """Long horizons of BASELINE.json configs[4] (T = 40, 80): fewer cases, the oracle QP has 6T unknowns.
+    python oracle/gen_golden.py --long"""
+    rh.setup()
+    z = np.load(os.path.join(REPO, "mpc_for_av_at_intersection_b200", "data", "intersection_routes.npz"))
+    routes_raw = [z[f"route_{i}"] for i in range(len(ROUTES))]
+    random_problems(40, routes_raw, n=96, seed=1040)
+    random_problems(80, routes_raw, n=48, seed=1080)
+    # one straight route and the scripted-obstacle left turn, truncated (every step is an independent check)
+    closed_loops(40, routes_raw, cases=[(ROUTES.index((2, 2)), False), (ROUTES.index((4, 1)), True)], max_steps=60)
+    closed_loops(80, routes_raw, cases=[(ROUTES.index((4, 1)), True)], max_steps=30)
+
+
 if __name__ == "__main__":
-    main()
+    if "--long" in sys.argv:
+        main_long()
+    else:
+        main()

@@ -153,36 +153,52 @@ def _ipm_ineq(H, g, G, h, tol, max_iter):
     return w, s, lam, status, it
 
 
-def _polish_ineq(H, g, G, h, w, lam):
-    """Active-set refinement on the reduced problem; dependent active rows are dropped by pivoted QR."""
+def _polish_ineq(H, g, G, h, w, lam, max_rounds=60):
+    """Active-set refinement on the reduced problem.
+
+    Starts from the interior point's guess (lam > slack), solves the equality-constrained QP on that set and
+    then repairs the set until the full KKT certificate holds: the most violated inactive row is added, the most
+    negative multiplier is dropped (one change per round).  Dependent active rows are dropped by pivoted QR.
+    Accepted only with the certificate, so a returned point is the optimum of the (strictly convex) QP whatever
+    accuracy the interior point stopped at."""
     import scipy.linalg as sla
-    slack = h - G @ w
-    active = np.where(lam > slack)[0]
     n = H.shape[0]
-    if len(active):
-        Ga = G[active]
-        _, R, piv = sla.qr(Ga.T, mode="economic", pivoting=True)
-        diag = np.abs(np.diag(R))
-        rank = int((diag > 1e-9 * max(diag.max(initial=0.0), 1e-300)).sum())
-        active = active[np.sort(piv[:rank])]
-    Ga = G[active]
-    k = len(active)
-    K = np.zeros((n + k, n + k))
-    K[:n, :n] = H
-    K[:n, n:] = Ga.T
-    K[n:, :n] = Ga
-    try:
-        sol = np.linalg.solve(K, np.concatenate([-g, h[active]]))
-        res = np.concatenate([-g, h[active]]) - K @ sol
-        sol = sol + np.linalg.solve(K, res)
-    except np.linalg.LinAlgError:
-        return w, lam, False
-    w2 = sol[:n]
-    lam2 = np.zeros_like(lam)
-    lam2[active] = sol[n:]
-    viol = max(0.0, float((G @ w2 - h).max(initial=0.0)))
-    if viol < 1e-9 and lam2.min(initial=0.0) > -1e-7 * (1.0 + np.abs(lam2).max(initial=0.0)):
-        return w2, lam2, True
+    slack = h - G @ w
+    active = set(np.where(lam > slack)[0].tolist())
+    hscale = 1.0 + np.abs(h)
+    for _ in range(max_rounds):
+        act = np.array(sorted(active), dtype=int)
+        if len(act):
+            Ga = G[act]
+            _, R, piv = sla.qr(Ga.T, mode="economic", pivoting=True)
+            diag = np.abs(np.diag(R))
+            rank = int((diag > 1e-9 * max(diag.max(initial=0.0), 1e-300)).sum())
+            act = act[np.sort(piv[:rank])]
+        Ga = G[act]
+        k = len(act)
+        K = np.zeros((n + k, n + k))
+        K[:n, :n] = H
+        K[:n, n:] = Ga.T
+        K[n:, :n] = Ga
+        rhs = np.concatenate([-g, h[act]])
+        try:
+            sol = np.linalg.solve(K, rhs)
+            sol = sol + np.linalg.solve(K, rhs - K @ sol)
+        except np.linalg.LinAlgError:
+            return w, lam, False
+        w2 = sol[:n]
+        lam2 = np.zeros_like(lam)
+        lam2[act] = sol[n:]
+        viol = (G @ w2 - h) / hscale
+        worst_v = int(np.argmax(viol)) if len(viol) else -1
+        lam_floor = -1e-7 * (1.0 + np.abs(lam2).max(initial=0.0))
+        worst_l = int(act[np.argmin(sol[n:])]) if k else -1
+        if (worst_v < 0 or viol[worst_v] < 1e-9) and (k == 0 or lam2[worst_l] > lam_floor):
+            return w2, lam2, True
+        if worst_v >= 0 and viol[worst_v] >= 1e-9:
+            active = set(act.tolist()) | {worst_v}
+        else:
+            active = set(act.tolist()) - {worst_l}
     return w, lam, False
 
 

@@ -63,7 +63,7 @@ def _compare(g, sel, out, T):
     assert e_dev < 1e-9
 
 
-@pytest.mark.parametrize("T", [13, 20])
+@pytest.mark.parametrize("T", [13, 20, 40, 80])      # 40, 80: the CTA-per-problem kernel (mpcb_step_long.cuh)
 def test_random_golden(T):
     g = golden(f"random_T{T}.npz")
     n = len(g["state"])
@@ -74,7 +74,7 @@ def test_random_golden(T):
     assert eng.launches >= 1
 
 
-@pytest.mark.parametrize("T", [13, 20])
+@pytest.mark.parametrize("T", [13, 20, 40, 80])
 def test_closed_loop_golden_per_step(T):
     """Every recorded MPC.step of the 13 reference closed loops, replayed as one batch."""
     g = golden(f"closed_loop_T{T}.npz")
