@@ -41,6 +41,7 @@ struct mpcb_handle {
     int variant = 0;             // kernel tuning variant (MPCB_VARIANT, only in MPCB_TUNE_VARIANTS builds)
     int* len_dev = nullptr;
     double* pathcc_dev = nullptr;    // [R][2 circles][x|y][ncmax]
+    double* ramp_dev = nullptr;      // [ncmax] np.cumsum(zeros + MAX_ACCEL): the ego prediction's acceleration ramp
     std::vector<int> len_host;
     std::vector<double> goal_host;   // [R,2] last point of each full course (mpc.py:263)
     // resident session: the [B,...] mirror of the reference's MPC object state lives on the device
@@ -263,6 +264,7 @@ void mpcb_destroy(mpcb_handle* h) {
     if (h->dl_dev) cudaFree(h->dl_dev);
     if (h->len_dev) cudaFree(h->len_dev);
     if (h->pathcc_dev) cudaFree(h->pathcc_dev);
+    if (h->ramp_dev) cudaFree(h->ramp_dev);
     if (h->ses.slab) cudaFree(h->ses.slab);
     if (h->ses.pin) cudaFreeHost(h->ses.pin);
     if (h->stage.pinned) cudaFreeHost(h->stage.pinned);
@@ -320,6 +322,13 @@ int mpcb_set_courses_host(mpcb_handle* h, const double* courses_host, const int*
         if (h->pathcc_dev) { cudaFree(h->pathcc_dev); h->pathcc_dev = nullptr; }
         CUDA_TRY(h, cudaMalloc(&h->pathcc_dev, cc.size() * sizeof(double)));
         CUDA_TRY(h, cudaMemcpy(h->pathcc_dev, cc.data(), cc.size() * sizeof(double), cudaMemcpyHostToDevice));
+        // np.cumsum(np.zeros(n) + MAX_ACCEL) (mpc_intersection.py:111-112): sequential float64 sums, index-only
+        std::vector<double> ramp((size_t)ncmax);
+        double acc = 0.0;
+        for (int i = 0; i < ncmax; ++i) { acc = acc + c.max_accel; ramp[i] = acc; }
+        if (h->ramp_dev) { cudaFree(h->ramp_dev); h->ramp_dev = nullptr; }
+        CUDA_TRY(h, cudaMalloc(&h->ramp_dev, ramp.size() * sizeof(double)));
+        CUDA_TRY(h, cudaMemcpy(h->ramp_dev, ramp.data(), ramp.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
     h->R = R; h->ncmax = ncmax;
     return MPCB_OK;
@@ -665,7 +674,7 @@ extern "C" {
 namespace {
 int launch_coupling(mpcb_handle* h, CouplingParams& p, cudaStream_t st) {
     const mpcb_config& c = h->cfg;
-    p.ncmax = h->ncmax; p.courses = h->courses_dev; p.pathcc = h->pathcc_dev; p.course_len = h->len_dev; p.dl = h->dl_dev;
+    p.ncmax = h->ncmax; p.courses = h->courses_dev; p.pathcc = h->pathcc_dev; p.accel_ramp = h->ramp_dev; p.course_len = h->len_dev; p.dl = h->dl_dev;
     const double along = c.car_length / 2 - c.car_width / 2, mid = c.wheelbase / 2;
     p.circ[0] = mid + along; p.circ[1] = mid - along;
     p.radius = c.car_width / sqrt(2.0);                          // width / 2**.5 (car_dimensions.py:64-65)

@@ -20,6 +20,7 @@ struct CouplingParams {
     int B, ncmax, vehicles_per_scenario;   // vehicles_per_scenario > 0: obstacles = the other egos of the scenario
     const double* courses;       // [R][3][ncmax]
     const double* pathcc;        // [R][2 circles][2 (x|y)][ncmax] circle centres of every path point (host-computed)
+    const double* accel_ramp;    // [ncmax] np.cumsum(zeros + MAX_ACCEL) (host-computed, sequential sums)
     const int* course_len;       // [R]
     const double* dl;            // [R]
     const double* state;         // [B,4] x y yaw v
@@ -46,7 +47,7 @@ struct CouplingParams {
 namespace mpcb {
 
 struct CouplingSmem {
-    double cum[32];                                        // chunk of the sequential cumulative distance
+    double cum[32];                                        // chunk of segment lengths, overwritten by their running sum
     int res_idx[MPCB_CP_MAX_RES];                          // path index of every kept ego frame
     double ocx[MPCB_CP_MAX_OBS][2][MPCB_CP_FRAMES];        // obstacle circle centres per frame
     double ocy[MPCB_CP_MAX_OBS][2][MPCB_CP_FRAMES];
@@ -108,7 +109,7 @@ __global__ void __launch_bounds__(WARPS * 32) coupling_kernel(const CouplingPara
     {
         const bool ramp = v0 < p.max_speed;
         const double dl_const = __dmul_rn(p.dt, p.max_speed);
-        double acc = 0.0, acc_a = 0.0;
+        double acc = 0.0;
         long long q_carry = 0;
         for (int base = 0; base < n; base += 32) {
             const int i = base + lane;
@@ -121,13 +122,16 @@ __global__ void __launch_bounds__(WARPS * 32) coupling_kernel(const CouplingPara
             __syncwarp();
             sm.cum[lane] = dist;
             __syncwarp();
-            double mycum = 0.0, mya = 0.0;
+            // np.cumsum is sequential: every lane runs the same chain of 32 additions and publishes each partial sum
+            // (uniform store), then picks its own -- cheaper than a select per step
 #pragma unroll 8
-            for (int j = 0; j < 32; ++j) {                         // np.cumsum is sequential
+            for (int j = 0; j < 32; ++j) {
                 acc = __dadd_rn(acc, sm.cum[j]);
-                acc_a = __dadd_rn(acc_a, p.max_accel);
-                if (j == lane) { mycum = acc; mya = acc_a; }
+                sm.cum[j] = acc;
             }
+            __syncwarp();
+            const double mycum = sm.cum[lane];
+            const double mya = valid ? p.accel_ramp[i] : 0.0;
             const double dl_i = ramp ? __dmul_rn(p.dt, fmin(__dadd_rn(mya, v0), p.max_speed)) : dl_const;
             const long long q = valid ? (long long)floor(__ddiv_rn(mycum, dl_i)) : 0;
             long long qprev = __shfl_up_sync(MPCB_FULL, q, 1);
@@ -148,6 +152,7 @@ __global__ void __launch_bounds__(WARPS * 32) coupling_kernel(const CouplingPara
     if (p.vehicles_per_scenario > 0) n_o = p.vehicles_per_scenario - 1;
     else n_o = p.n_obs ? p.n_obs[b] : 0;
     n_o = min(n_o, MPCB_CP_MAX_OBS);
+    double ov0 = 0.0, oa0 = 0.0, ox0 = 0.0, oy0 = 0.0;
     if (lane < n_o) {
         double ox, oy, ov, oyaw, oa, ost;
         if (p.vehicles_per_scenario > 0) {          // the other egos of this scenario, constant speed, zero steer
@@ -159,19 +164,49 @@ __global__ void __launch_bounds__(WARPS * 32) coupling_kernel(const CouplingPara
             const double* o6 = p.obs + ((size_t)b * MPCB_CP_MAX_OBS + lane) * 6;
             ox = o6[0]; oy = o6[1]; ov = o6[2]; oyaw = o6[3]; oa = o6[4]; ost = o6[5];
         }
+        // pass A (sequential per obstacle): the yaw and speed sequences.  x, y of frame f use the OLD v / yaw, the
+        // yaw update uses the NEW v (moving_obstacles_prediction.py:33-40); yaw_0..yaw_nf go to ocx[o][0][f]
+        // (the last one to ocx[o][1][nf-1]) so that pass B can take their sines and cosines in parallel
         const double tn = tan(ost);
+        ov0 = ov; oa0 = oa; ox0 = ox; oy0 = oy;
         for (int f = 0; f < p.n_frames; ++f) {
-            double sn, cs;
-            sincos(oyaw, &sn, &cs);
-            ox = __dadd_rn(ox, __dmul_rn(__dmul_rn(ov, cs), p.dt));
-            oy = __dadd_rn(oy, __dmul_rn(__dmul_rn(ov, sn), p.dt));
+            sm.ocx[lane][0][f] = oyaw;
             ov = __dadd_rn(ov, __dmul_rn(oa, p.dt));
             oyaw = __dadd_rn(oyaw, __dmul_rn(__dmul_rn(__ddiv_rn(ov, p.wheelbase), tn), p.dt));
-            sincos(oyaw, &sn, &cs);
+        }
+        sm.ocx[lane][1][p.n_frames - 1] = oyaw;
+    }
+    __syncwarp();
+    // pass B (parallel): sin / cos of all (obstacle, frame) yaws, in place: cos -> ocx, sin -> ocy
+    {
+        const int nf1 = p.n_frames + 1, total = n_o * nf1;
+        for (int idx = lane; idx < total; idx += 32) {
+            const int o = idx / nf1, f = idx - o * nf1;
+            double* px = f < p.n_frames ? &sm.ocx[o][0][f] : &sm.ocx[o][1][p.n_frames - 1];
+            double* py = f < p.n_frames ? &sm.ocy[o][0][f] : &sm.ocy[o][1][p.n_frames - 1];
+            double sn, cs;
+            sincos(*px, &sn, &cs);
+            *px = cs; *py = sn;
+        }
+    }
+    __syncwarp();
+    // pass C (sequential per obstacle): positions and circle centres; frame f overwrites slot f after reading it
+    double bx0 = 1e300, bx1 = -1e300, by0 = 1e300, by1 = -1e300;       // bounding box of this obstacle's circle centres
+    if (lane < n_o) {
+        double ox = ox0, oy = oy0, ov = ov0;
+        const int nf = p.n_frames;
+        for (int f = 0; f < nf; ++f) {
+            const double cs = sm.ocx[lane][0][f], sn = sm.ocy[lane][0][f];
+            const double cs2 = f + 1 < nf ? sm.ocx[lane][0][f + 1] : sm.ocx[lane][1][nf - 1];
+            const double sn2 = f + 1 < nf ? sm.ocy[lane][0][f + 1] : sm.ocy[lane][1][nf - 1];
+            ox = __dadd_rn(ox, __dmul_rn(__dmul_rn(ov, cs), p.dt));
+            oy = __dadd_rn(oy, __dmul_rn(__dmul_rn(ov, sn), p.dt));
+            ov = __dadd_rn(ov, __dmul_rn(oa0, p.dt));
 #pragma unroll
             for (int c = 0; c < 2; ++c) {           // trajectories.py:28-34 with y_offset = 0
-                sm.ocx[lane][c][f] = __dadd_rn(__dmul_rn(cs, p.circ[c]), ox);
-                sm.ocy[lane][c][f] = __dadd_rn(__dmul_rn(sn, p.circ[c]), oy);
+                const double qx = __dadd_rn(__dmul_rn(cs2, p.circ[c]), ox), qy = __dadd_rn(__dmul_rn(sn2, p.circ[c]), oy);
+                sm.ocx[lane][c][f] = qx; sm.ocy[lane][c][f] = qy;
+                bx0 = fmin(bx0, qx); bx1 = fmax(bx1, qx); by0 = fmin(by0, qy); by1 = fmax(by1, qy);
             }
         }
     }
@@ -189,7 +224,14 @@ __global__ void __launch_bounds__(WARPS * 32) coupling_kernel(const CouplingPara
             const int g = min(f, nf - 1);
             for (int a = 0; a < 2 && !hit; ++a) {
                 const double ax = pcc[(2 * a) * p.ncmax + pidx], ay = pcc[(2 * a + 1) * p.ncmax + pidx];
-                for (int o = 0; o < n_o && !hit; ++o) {
+                // obstacles whose circle centres (any frame) can be within reach of this ego circle: a conservative
+                // box test per lane/obstacle; the exact test below runs only for those, in ascending obstacle order
+                const double mrg = thr * (1.0 + 1e-9);
+                unsigned cand = __ballot_sync(MPCB_FULL, lane < n_o && ax >= bx0 - mrg && ax <= bx1 + mrg &&
+                                                             ay >= by0 - mrg && ay <= by1 + mrg);
+                while (cand && !hit) {
+                    const int o = __ffs(cand) - 1;
+                    cand &= cand - 1;
                     for (int base = 0; base < 2 * W; base += 32) {
                         const int idx = base + lane;
                         bool h = false;
