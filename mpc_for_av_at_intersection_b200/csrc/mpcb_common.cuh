@@ -99,4 +99,11 @@ __device__ __forceinline__ void sts_pair_if(bool pred, double* ptr, double x, do
                  :: "r"(addr), "d"(x), "d"(y), "r"((int)pred) : "memory");
 }
 
+// FP64 tensor-core tile: D(8x8) += A(8x4) * B(4x8).  Lane l holds A[l/4][l%4], B[l%4][l/4] and the two
+// accumulator entries D[l/4][2*(l%4)], D[l/4][2*(l%4)+1] (PTX mma.sync.aligned.m8n8k4.row.col.f64).
+__device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
 }  // namespace mpcb

@@ -547,28 +547,60 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
             {
                 // steer block: assembled only now (the accel rows are dead), rank-T update C -= L21 D^-1 L21',
                 // then its own LDL'
-                double C[T];
-#pragma unroll
-                for (int j = 0; j < T; ++j) C[j] = sm.HC[SM::colB(j) + lane];
+                // The rank-T update runs on the FP64 tensor cores: S = -L21 D^-1 L21' as 8x8 tiles of
+                // mma.m8n8k4 (lower tiles only), operands gathered straight from the stored cross factor -- no operand
+                // broadcast through the LSU, 256 FMAs per instruction.  The tiles go through a scratch square (the
+                // steer factor's storage, dead until the LDL' below) to reach the lane-per-row layout.
                 __syncwarp();
-                auto syrk = [&](int k0, int k1, auto odd_base) {          // columns with an odd base shift the pairs
-                    constexpr bool ODD = decltype(odd_base)::value;
-#pragma unroll 1
-                    for (int k = k0; k < k1; ++k) {
-                        const double* col = &sm.LB[k * SM::SB + (ODD ? 1 : 0)];
-                        const double lb = col[lane] * sm.iz[k].x;
-                        if (ODD) C[0] -= lb * col[0];
+                {
+                    constexpr int NTL = (T + 7) / 8;                       // 8-row tiles
+                    constexpr int KB = (T + 3) / 4;                        // 4-pivot blocks
+                    double acc[NTL * (NTL + 1) / 2][2];
 #pragma unroll
-                        for (int j = ODD ? 1 : 0; j + 1 < T; j += 2) {
-                            const double2 c = *reinterpret_cast<const double2*>(col + j);
-                            C[j] -= lb * c.x; C[j + 1] -= lb * c.y;
+                    for (int t = 0; t < NTL * (NTL + 1) / 2; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+                    const int fr = lane >> 2, fk = lane & 3;              // fragment row / k index of this lane
+#pragma unroll 1
+                    for (int kb = 0; kb < KB; ++kb) {
+                        const int k = 4 * kb + fk;
+                        const bool kv = (T % 4 == 0) || k < T;
+                        const int kc = kv ? k : 0;
+                        const double* col = &sm.LB[SM::colB(kc) + fr];
+                        const double ivk = sm.iz[kc].x;
+                        double fa[NTL], fb[NTL];
+#pragma unroll
+                        for (int x = 0; x < NTL; ++x) {
+                            const double raw = col[8 * x];                 // rows >= T: pad / next column, dead entries only
+                            fb[x] = kv ? raw : 0.0;
+                            fa[x] = kv ? -raw * ivk : 0.0;
                         }
-                        if (((T - (ODD ? 1 : 0)) & 1)) C[T - 1] -= lb * col[T - 1];
+#pragma unroll
+                        for (int I = 0; I < NTL; ++I)
+#pragma unroll
+                            for (int J = 0; J <= I; ++J) dmma_m8n8k4(acc[I * (I + 1) / 2 + J][0], acc[I * (I + 1) / 2 + J][1], fa[I], fb[J]);
                     }
-                };
-                syrk(0, T < 8 ? T : 8, std::false_type{});
-                if (T > 8) syrk(8, T < 16 ? T : 16, std::true_type{});
-                if (T > 16) syrk(16, T, std::false_type{});
+                    double* S = sm.LC;                                     // [row][SB], rows and columns < T
+#pragma unroll
+                    for (int I = 0; I < NTL; ++I)
+#pragma unroll
+                        for (int J = 0; J <= I; ++J) {
+                            const int r = 8 * I + fr, c = 8 * J + 2 * fk;
+                            if (r < T && c + 1 < T + (T & 1)) *reinterpret_cast<double2*>(&S[r * SM::SB + c]) =
+                                make_double2(acc[I * (I + 1) / 2 + J][0], acc[I * (I + 1) / 2 + J][1]);
+                        }
+                }
+                __syncwarp();
+                double C[T];
+                {
+                    const double* Sr = &sm.LC[(act ? lane : 0) * SM::SB];
+#pragma unroll
+                    for (int j = 0; j + 1 < T; j += 2) {                  // entries above the diagonal are never used
+                        const double2 sv = *reinterpret_cast<const double2*>(Sr + j);
+                        C[j] = sm.HC[SM::colB(j) + lane] + sv.x;
+                        C[j + 1] = sm.HC[SM::colB(j + 1) + lane] + sv.y;
+                    }
+                    if (T & 1) C[T - 1] = sm.HC[SM::colB(T - 1) + lane] + Sr[T - 1];
+                }
+                __syncwarp();                                              // the scratch is overwritten by the factor below
                 double c0 = C[0] + (lane == 0 ? dC : 0.0) - (lane == 1 ? wr_prev : 0.0);
                 double ivm = rcp(c0);
                 constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
