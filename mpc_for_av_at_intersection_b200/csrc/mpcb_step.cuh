@@ -144,6 +144,130 @@ __device__ __forceinline__ void ldl_steer_steps(WarpSmem<T>& sm, double (&C)[T],
     }
 }
 
+// ---- blocked accel + cross phase on the FP64 tensor cores ---------------------------------------------------------
+// The accel block A (lower 8x8 tiles) and the cross block B (all tiles) live in mma.m8n8k4 accumulator fragments.
+// Per panel of four pivots: (1) the lanes that hold the panel's columns drop them into a [row][4] buffer, (2) in the
+// lane-per-row view the 4x4 pivot block is eliminated with shuffles (the predictor's forward solve rides along) and
+// the finished columns are published for the triangular solves, (3) the trailing tiles get one rank-4 update each
+// from register fragments: A -= L U', B -= L21 U' with L = scaled panel rows, U = unscaled ones.  Compared with the
+// lane-per-row rank-1 updates this removes the operand broadcast through the LSU (one wavefront per double) and
+// issues 256 FMAs per instruction.
+template <int T>
+__device__ __forceinline__ void ldl_accel_blocked(WarpSmem<T>& sm, int lane, bool act, double wv_suf, double dA,
+                                                  double& ra, double& rdl, bool& bad, double& inva) {
+    using SM = WarpSmem<T>;
+    constexpr int NTL = (T + 7) / 8, KB = (T + 3) / 4, NTA = NTL * (NTL + 1) / 2, PR = 8 * NTL;
+    const int fr = lane >> 2, fk = lane & 3;
+    double* const PA = sm.LC;                       // [PR][4] panel rows of A: in entries, out -L (scaled)
+    double* const PQ = sm.LC + PR * 4;              // same for the cross block
+    double* const PU = sm.LC + 2 * PR * 4;          // unscaled panel rows of A (the B fragments)
+    double* const tw = sm.bc[0];                    // per-stage G'WG terms by index
+    double* const td = sm.bc[1];
+    if (act) { tw[lane] = wv_suf; td[lane] = dA; }
+    if (lane < 4 * (PR - T)) {                      // pad rows of the fragment buffers stay zero
+        const int o = (T + (lane >> 2)) * 4 + (lane & 3);
+        PA[o] = 0.0; PQ[o] = 0.0; PU[o] = 0.0;
+    }
+    __syncwarp();
+    double At[NTA][2], Qt[NTL][NTL][2];
+#pragma unroll
+    for (int I = 0; I < NTL; ++I)
+#pragma unroll
+        for (int J = 0; J < NTL; ++J)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int i = 8 * I + fr, j = 8 * J + 2 * fk + e;
+                const bool ok = i < T && j < T;
+                const int ic = ok ? i : 0, jc = ok ? j : 0;
+                Qt[I][J][e] = ok ? sm.HB[SM::colB(jc) + ic] : 0.0;
+                if (J <= I) {
+                    const int mx = ic > jc ? ic : jc;
+                    const double v = sm.HA[SM::colB(jc) + ic] + tw[mx] + (ic == jc ? td[ic] : 0.0);
+                    At[I * (I + 1) / 2 + J][e] = ok ? v : 0.0;
+                }
+            }
+    const int row = act ? lane : 0;
+#pragma unroll
+    for (int p = 0; p < KB; ++p) {
+        constexpr int dummy = 0; (void)dummy;
+        const int J = p >> 1, h = p & 1;
+        const bool holder = (fk >> 1) == h;
+        // (1) panel columns -> [row][4]
+#pragma unroll
+        for (int I = 0; I < NTL; ++I) {
+            const int r = 8 * I + fr;
+            if (holder && r < T) {
+                if (I >= J) *reinterpret_cast<double2*>(&PA[r * 4 + 2 * (fk & 1)]) = make_double2(At[I * (I + 1) / 2 + J][0], At[I * (I + 1) / 2 + J][1]);
+                *reinterpret_cast<double2*>(&PQ[r * 4 + 2 * (fk & 1)]) = make_double2(Qt[I][J][0], Qt[I][J][1]);
+            }
+        }
+        __syncwarp();
+        // (2) lane-per-row elimination of the 4x4 pivot block
+        double a[4], q[4], ln[4], lqn[4], un[4];
+        {
+            const double2 a01 = *reinterpret_cast<const double2*>(&PA[row * 4]), a23 = *reinterpret_cast<const double2*>(&PA[row * 4 + 2]);
+            const double2 q01 = *reinterpret_cast<const double2*>(&PQ[row * 4]), q23 = *reinterpret_cast<const double2*>(&PQ[row * 4 + 2]);
+            a[0] = a01.x; a[1] = a01.y; a[2] = a23.x; a[3] = a23.y;
+            q[0] = q01.x; q[1] = q01.y; q[2] = q23.x; q[3] = q23.y;
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int k = 4 * p + c;
+            if (k < T) {
+                const double dk = shfl(a[c], k);
+                bad = bad || !(dk > 0.0);
+                const double iv = rcp(dk);
+                const bool mine = lane == k;
+                inva = mine ? iv : inva;
+                const double a0s = (act && lane > k) ? a[c] : 0.0;
+                const double q0 = act ? q[c] : 0.0;
+                const double la = a0s * iv, lq = q0 * iv;
+                const double zk = shfl(ra, k) * iv;
+                ra = fma(-a0s, zk, ra);
+                rdl = fma(-q0, zk, rdl);
+#pragma unroll
+                for (int c2 = c + 1; c2 < 4; ++c2) {
+                    if (4 * p + c2 < T) {
+                        const double u = shfl(a[c], 4 * p + c2);
+                        a[c2] = fma(-la, u, a[c2]);
+                        q[c2] = fma(-lq, u, q[c2]);
+                    }
+                }
+                sm.LA[SM::colL(k) + lane] = a0s; sm.LB[SM::colB(k) + lane] = q0;      // idle lanes: see ldl_accel_steps
+                sts_pair_if(mine, &sm.iz[k].x, iv, 0.0);
+                ln[c] = -la; lqn[c] = -lq; un[c] = a0s;
+            } else { ln[c] = 0.0; lqn[c] = 0.0; un[c] = 0.0; }
+        }
+        constexpr bool dummy2 = true; (void)dummy2;
+        const int J0 = J + h;                          // first column tile that still has live columns
+        if (J0 < NTL) {
+            if (act) {
+                *reinterpret_cast<double2*>(&PA[row * 4]) = make_double2(ln[0], ln[1]); *reinterpret_cast<double2*>(&PA[row * 4 + 2]) = make_double2(ln[2], ln[3]);
+                *reinterpret_cast<double2*>(&PQ[row * 4]) = make_double2(lqn[0], lqn[1]); *reinterpret_cast<double2*>(&PQ[row * 4 + 2]) = make_double2(lqn[2], lqn[3]);
+                *reinterpret_cast<double2*>(&PU[row * 4]) = make_double2(un[0], un[1]); *reinterpret_cast<double2*>(&PU[row * 4 + 2]) = make_double2(un[2], un[3]);
+            }
+            __syncwarp();
+            // (3) rank-4 updates of the trailing tiles
+            double fa[NTL], fq[NTL], fb[NTL];
+#pragma unroll
+            for (int X = 0; X < NTL; ++X) {
+                fa[X] = PA[(8 * X + fr) * 4 + fk]; fq[X] = PQ[(8 * X + fr) * 4 + fk]; fb[X] = PU[(8 * X + fr) * 4 + fk];
+            }
+#pragma unroll
+            for (int Jp = 0; Jp < NTL; ++Jp) {
+                if (Jp >= J0) {
+#pragma unroll
+                    for (int I = 0; I < NTL; ++I) {
+                        if (I >= Jp) dmma_m8n8k4(At[I * (I + 1) / 2 + Jp][0], At[I * (I + 1) / 2 + Jp][1], fa[I], fb[Jp]);
+                        dmma_m8n8k4(Qt[I][Jp][0], Qt[I][Jp][1], fq[I], fb[Jp]);
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
+
 // top-3 insertion keeping (d, idx) ascending; ties keep the earlier (lower) index first
 __device__ __forceinline__ void top3_insert(double d, int i, double (&bd)[3], int (&bi)[3]) {
     if (d < bd[2]) {
@@ -529,6 +653,12 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
             bool bad = false;
             double inva = 0.0, invd = 0.0;
             {
+#ifdef MPCB_BLOCKED_ACCEL
+                // measured alternative (profiles/r01b_NOTES.md): 17 % fewer instructions, but the panel elimination puts
+                // shuffle -> reciprocal -> shuffle chains and two shared-memory round trips per panel on the critical
+                // path; 9 % slower at two resident warps per scheduler
+                ldl_accel_blocked<T>(sm, lane, act, wv_suf, dA, ra, rdl, bad, inva);
+#else
                 double R[T], Q[T];                               // accel-block row and cross-block row of this lane
 #pragma unroll
                 for (int j = 0; j < T; ++j) {                    // idle lanes read valid memory, their rows are never used
@@ -543,6 +673,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                 ldl_accel_steps<T, T - 1 - K1>(sm, R, Q, K1, K2, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
                 ldl_accel_steps<T, T - 1 - K2>(sm, R, Q, K2, K3, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
                 ldl_accel_steps<T, T - 1 - K3>(sm, R, Q, K3, T, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
+#endif
             }
             {
                 // steer block: assembled only now (the accel rows are dead), rank-T update C -= L21 D^-1 L21',
