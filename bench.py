@@ -100,23 +100,27 @@ class ClockSampler:
 
 
 def cpu_arm(args, courses, cfg, per_core_problems, steps_each, cores=None):
-    """Time the oracle port on a bounded sample of the bench workload.  Returns (dict, solves/s)."""
+    """Time the CPU port (oracle/mpc_port.cpp, all host cores) on a bounded sample of the bench workload.
+    Returns (dict, solves/s)."""
     sys.path.insert(0, os.path.join(REPO, "oracle"))
     import cpu_baseline
     from mpc_for_av_at_intersection_b200.scenarios import make_workload
     cores = cores or os.cpu_count() or 1
-    n = per_core_problems * cores
+    n = min(args.batch, 4096)
     wl = make_workload(courses, n, seed=args.seed, first=0)
-    r = cpu_baseline.run(courses, wl, range(n), steps_each, cfg.T, cfg.wheelbase, cfg.dt, cores=cores)
+    cpu_baseline.run_cpp(courses, wl, min(n, 64), 1, cfg, cores=cores)          # load / page in
+    r = cpu_baseline.run_cpp(courses, wl, n, steps_each, cfg, cores=cores)
     v = r["solves"] / r["seconds"]
     return ({"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port",
              "sample": f"first {n} problems of the workload x {steps_each} closed-loop steps = {r['solves']} solves "
-                       f"in {r['seconds']:.1f} s wall ({sum(r['per_core_busy_s']):.1f} core-s), numpy float64 "
-                       f"oracle port (cvxpy+ECOS and /root/reference are not on this box)"}, v)
+                       f"in {r['seconds']:.1f} s wall on {r['cores']} threads; plain C++ float64 port oracle/mpc_port.cpp "
+                       f"(generic dense condensing + dense Mehrotra IPM in place of cvxpy+ECOS, which like "
+                       f"/root/reference is not on this box)"}, v)
 
 
 def run_reference(args):
-    """--impl reference: the CPU port on all host cores; each step = a bounded sample of the workload."""
+    """--impl reference: the CPU port on all host cores; a step = one control step of a bounded sample (<= 4096
+    problems) of the same workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
@@ -125,16 +129,17 @@ def run_reference(args):
     import cpu_baseline
     from mpc_for_av_at_intersection_b200.scenarios import make_workload
     cfg = MpcConfig.from_json(T=args.horizon)
-    courses = CourseSet(load_intersection_routes(), smooth=False)   # the port smooths its own copy (mpc.py:257)
+    courses = CourseSet(load_intersection_routes())
     cores = os.cpu_count() or 1
-    per_step = args.ref_problems_per_core * cores         # problems solved once per "step"
+    per_step = min(args.batch, 4096) if cfg.T <= 20 else min(args.batch, 256)
     wl = make_workload(courses, per_step, seed=args.seed, first=0)
-    # one pool run of (warmup + steps) closed-loop control steps; the first `warmup` are not separable per
-    # problem inside a worker, so time two runs: W steps (discarded) then K steps
     if args.warmup > 0:
-        cpu_baseline.run(courses, wl, range(min(per_step, cores)), 1, cfg.T, cfg.wheelbase, cfg.dt, cores=cores)
-    r = cpu_baseline.run(courses, wl, range(per_step), args.steps, cfg.T, cfg.wheelbase, cfg.dt, cores=cores)
+        cpu_baseline.run_cpp(courses, wl, per_step, min(args.warmup, 3), cfg, cores=cores)
+    r = cpu_baseline.run_cpp(courses, wl, per_step, args.steps, cfg, cores=cores)
     v = r["solves"] / r["seconds"]
+    sample = (f"{per_step} problems x {args.steps} closed-loop steps = {r['solves']} solves in {r['seconds']:.1f} s wall on "
+              f"{r['cores']} threads; plain C++ float64 port of main/lib/mpc.py (oracle/mpc_port.cpp: generic dense condensing + "
+              f"dense Mehrotra IPM; the reference's cvxpy+ECOS stack is not installable offline), {r['failed']} failed solves")
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * r["seconds"] / max(args.steps, 1), "higher_is_better": True,
@@ -142,10 +147,7 @@ def run_reference(args):
         "config": {"workload": f"BASELINE.json configs[1]: independent ego vehicles on randomised intersection "
                                f"scenarios, horizon N={cfg.T}, closed loop; bounded sample of {per_step} problems "
                                f"per step", "horizon": cfg.T, "problems_per_step": per_step, "seed": args.seed},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port",
-                         "sample": f"{per_step} problems x {args.steps} closed-loop steps = {r['solves']} solves in "
-                                   f"{r['seconds']:.1f} s wall; numpy float64 oracle port of main/lib/mpc.py "
-                                   f"(the reference's cvxpy+ECOS stack is not installable offline)"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -182,8 +184,7 @@ def run_b200(args):
     # ---- CPU baseline first (fork pool before CUDA is initialised), rank 0 at N=1 only ---------------------
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        cpu, _ = cpu_arm(args, CourseSet(load_intersection_routes(), smooth=False), cfg,
-                         args.cpu_problems_per_core, args.cpu_steps)
+        cpu, _ = cpu_arm(args, courses, cfg, args.cpu_problems_per_core, args.cpu_steps)
 
     import numpy as np
     import torch
@@ -331,7 +332,7 @@ def main():
     ap.add_argument("--seed", type=int, default=1235)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-problems-per-core", type=int, default=4)
-    ap.add_argument("--cpu-steps", type=int, default=6)
+    ap.add_argument("--cpu-steps", type=int, default=12, help="closed-loop steps of the cpu_baseline sample (<= 4096 problems)")
     ap.add_argument("--ref-problems-per-core", type=int, default=2)
     args = ap.parse_args()
     if args.warmup < 3:

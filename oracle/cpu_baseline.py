@@ -71,3 +71,32 @@ def run(courses, workload, ids, steps, T, L, dt, cores=None):
     solves = sum(r[0] for r in res)
     controls = sorted(sum((r[2] for r in res), []))
     return dict(solves=solves, seconds=wall, cores=cores, per_core_busy_s=[r[1] for r in res], controls=controls)
+
+
+def run_cpp(courses_smoothed, workload, n, steps, cfg, cores=None):
+    """Same closed loops through the plain C++ port (oracle/mpc_port.cpp), `cores` std::threads inside one call per
+    control step; the plant step between calls is the vectorised host twin of Simulation.step.
+    `courses_smoothed`: CourseSet with smooth=True (the port, like MPC.__init__, works on smoothed yaws).
+    Returns dict(solves, seconds (wall), cores, failed)."""
+    import mpc_port
+    from mpc_for_av_at_intersection_b200.scenarios import host_plant_step
+    cores = int(cores or os.cpu_count() or 1)
+    T = int(cfg.T)
+    cfgvec = mpc_port.pack_config(cfg)
+    mpc_port.lib()
+    state = np.ascontiguousarray(workload["state"][:n]).copy()
+    route = np.ascontiguousarray(workload["route"][:n]).astype(np.int32)
+    ncourse = courses_smoothed.length[route].astype(np.int32)
+    target = np.ascontiguousarray(workload["target_ind"][:n]).astype(np.int32)
+    warm = np.zeros(n, np.int32)
+    oa = np.zeros((n, T)); od = np.zeros((n, T)); di_ai = np.zeros((n, 2))
+    L = np.full(n, float(cfg.wheelbase))
+    solves = failed = 0
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        out = mpc_port.step_batch(cfgvec, courses_smoothed.packed, courses_smoothed.dl, state, route, ncourse, L, target, warm,
+                                  oa, od, di_ai, want_traj=False, nthreads=cores)
+        solves += n
+        failed += int((out["status"] >= 2).sum())
+        state = host_plant_step(state, di_ai[:, 0], di_ai[:, 1], float(cfg.wheelbase), float(cfg.dt))
+    return dict(solves=solves, seconds=time.perf_counter() - t0, cores=cores, failed=failed)
