@@ -109,10 +109,10 @@ def cpu_arm(args, courses, cfg, per_core_problems, steps_each, cores=None):
     n = min(args.batch, 4096)
     wl = make_workload(courses, n, seed=args.seed, first=0)
     cpu_baseline.run_cpp(courses, wl, min(n, 64), 1, cfg, cores=cores)          # load / page in
-    r = cpu_baseline.run_cpp(courses, wl, n, steps_each, cfg, cores=cores)
+    r = cpu_baseline.run_cpp(courses, wl, n, steps_each, cfg, cores=cores, min_seconds=args.cpu_seconds)
     v = r["solves"] / r["seconds"]
     return ({"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port",
-             "sample": f"first {n} problems of the workload x {steps_each} closed-loop steps = {r['solves']} solves "
+             "sample": f"first {n} problems of the workload x {r['steps']} closed-loop steps = {r['solves']} solves "
                        f"in {r['seconds']:.1f} s wall on {r['cores']} threads; plain C++ float64 port oracle/mpc_port.cpp "
                        f"(generic dense condensing + dense Mehrotra IPM in place of cvxpy+ECOS, which like "
                        f"/root/reference is not on this box)"}, v)
@@ -334,6 +334,7 @@ def main():
     ap.add_argument("--cpu-problems-per-core", type=int, default=4)
     ap.add_argument("--cpu-steps", type=int, default=12, help="closed-loop steps of the cpu_baseline sample (<= 4096 problems)")
     ap.add_argument("--ref-problems-per-core", type=int, default=2)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="minimum wall time of the cpu_baseline sample")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -73,11 +73,12 @@ def run(courses, workload, ids, steps, T, L, dt, cores=None):
     return dict(solves=solves, seconds=wall, cores=cores, per_core_busy_s=[r[1] for r in res], controls=controls)
 
 
-def run_cpp(courses_smoothed, workload, n, steps, cfg, cores=None):
+def run_cpp(courses_smoothed, workload, n, steps, cfg, cores=None, min_seconds=0.0, max_steps=2000, reset_every=40):
     """Same closed loops through the plain C++ port (oracle/mpc_port.cpp), `cores` std::threads inside one call per
     control step; the plant step between calls is the vectorised host twin of Simulation.step.
     `courses_smoothed`: CourseSet with smooth=True (the port, like MPC.__init__, works on smoothed yaws).
-    Returns dict(solves, seconds (wall), cores, failed)."""
+    Runs at least `steps` control steps and keeps going until `min_seconds` of wall time have passed.
+    Returns dict(solves, seconds (wall), cores, failed, steps)."""
     import mpc_port
     from mpc_for_av_at_intersection_b200.scenarios import host_plant_step
     cores = int(cores or os.cpu_count() or 1)
@@ -93,10 +94,16 @@ def run_cpp(courses_smoothed, workload, n, steps, cfg, cores=None):
     L = np.full(n, float(cfg.wheelbase))
     solves = failed = 0
     t0 = time.perf_counter()
-    for _ in range(steps):
+    k = 0
+    while k < steps or (time.perf_counter() - t0 < min_seconds and k < max_steps):
+        if k and reset_every and k % reset_every == 0:          # start the same closed loops again (same mix of steps)
+            state = np.ascontiguousarray(workload["state"][:n]).copy()
+            target = np.ascontiguousarray(workload["target_ind"][:n]).astype(np.int32)
+            warm[:] = 0
+        k += 1
         out = mpc_port.step_batch(cfgvec, courses_smoothed.packed, courses_smoothed.dl, state, route, ncourse, L, target, warm,
                                   oa, od, di_ai, want_traj=False, nthreads=cores)
         solves += n
         failed += int((out["status"] >= 2).sum())
         state = host_plant_step(state, di_ai[:, 0], di_ai[:, 1], float(cfg.wheelbase), float(cfg.dt))
-    return dict(solves=solves, seconds=time.perf_counter() - t0, cores=cores, failed=failed)
+    return dict(solves=solves, seconds=time.perf_counter() - t0, cores=cores, failed=failed, steps=k)
