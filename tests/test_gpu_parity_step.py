@@ -83,3 +83,46 @@ def test_closed_loop_golden_per_step(T):
     sel = np.arange(n)
     out = _run_host(eng, g, sel)
     _compare(g, sel, out, T)
+
+
+def test_max_iter_3_matches_oracle():
+    """MAX_ITER > 1 (main/lib/mpc.py:211-239): every pass re-runs the reference lookup with the speeds of the previous
+    pass's solution (`ov`), the rollout with its inputs, and solves again.  The shipped config has MAX_ITER = 1, so
+    there is no golden vector for it; the numpy oracle (same loop, its own QP solver) is the checker."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+    import mpc_oracle as mo
+    from mpc_for_av_at_intersection_b200 import MpcConfig
+    from mpc_for_av_at_intersection_b200.batched import BatchedMPC, CourseSet
+    T, B = 13, 48
+    cfg = MpcConfig.from_json(T=T, MAX_ITER=3)
+    routes = load_routes(False)
+    cs = CourseSet(routes)
+    rng = np.random.default_rng(11)
+    route = rng.integers(0, len(routes), B).astype(np.int32)
+    idx0 = np.array([rng.integers(0, cs.length[r] - 150) for r in route])
+    state = np.zeros((B, 4))
+    for b in range(B):
+        x, y, yaw = cs.packed[route[b], :, idx0[b]]
+        lat = rng.normal(0, 0.3)
+        state[b] = (x - np.sin(yaw) * lat, y + np.cos(yaw) * lat, yaw + rng.normal(0, 0.05), rng.uniform(0, 8.0))
+    target = np.maximum(idx0 - 3, 0).astype(np.int32)
+    eng = BatchedMPC(cfg, cs, B)
+    warm = np.zeros(B, np.int32)
+    oa = np.zeros((B, T)); od = np.zeros((B, T)); di_ai = np.zeros((B, 2))
+    tgt = target.copy()
+    out = eng.step_host(state, route, cs.length[route].astype(np.int32), tgt, warm, oa, od, di_ai)
+    ocfg = mo.Cfg.from_dict({"T": T, "MAX_ITER": 3})
+    worst = 0.0
+    for b in range(B):
+        n = cs.length[route[b]]
+        om = mo.OracleMPC(cs.packed[route[b], 0, :n].copy(), cs.packed[route[b], 1, :n].copy(), cs.packed[route[b], 2, :n].copy(),
+                          float(cs.dl[route[b]]), 2.86, 0.2, ocfg)
+        om.target_ind = int(target[b])
+        di, ai = om.step(list(state[b]))
+        assert om.target_ind == tgt[b]
+        assert np.array_equal(om.xref, out["xref"][b]), "xref of the LAST pass, indices from the previous pass's speeds"
+        worst = max(worst, abs(di - di_ai[b, 0]), abs(ai - di_ai[b, 1]), np.abs(om.ox - out["traj"][b, 0]).max())
+    print(f"MAX_ITER=3: max deviation {worst:.2e}")
+    assert worst < 1e-6
