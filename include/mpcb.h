@@ -228,6 +228,27 @@ int mpcb_session_multi_agent_dev(mpcb_handle* h, int nsteps, int vehicles_per_sc
 #define MPCB_F_COLLIDED 16  /* int [B] */
 #define MPCB_F_COLL_IDX 17  /* int [B] */
 
+/* ---- scripted cross traffic on the device ------------------------------------------
+ * replaces: the `MovingObstacleTIntersection` objects of the reference scenario (main/lib/moving_obstacles.py:165-231,
+ * constructed at main/scenarios/mpc_intersection.py:41-44) and their part of the loop body -- `o.get()` feeding the
+ * predictions (:118-121) and `o.step()` after the solve (:154-156).
+ *   script_host [B, MPCB_MAX_OBSTACLES, 4]  constructor arguments per obstacle: direction (>= 0: from the left at
+ *               (-30, -3) heading 0; < 0: from the right at (30, 3) heading pi), turning (0/1), speed, offset
+ *               (seconds before it starts moving; <= 0 = None).  dt and the wheelbase are the handle's.
+ *   n_obs_host  [B] obstacles of each ego's scenario (0..MPCB_MAX_OBSTACLES)
+ * Resets every script to its constructor state (counter = 0).  Synchronous. */
+int mpcb_session_set_scripted_host(mpcb_handle* h, const double* script_host, const int* n_obs_host);
+/* replaces: the whole loop body of main/scenarios/mpc_intersection.py:95-159 WITH its scripted obstacles, nsteps times,
+ * with no host round trip: per control step one coupling launch (is_goal | obstacle get() + step() | nearest index |
+ * predictions | first collision | path cut) and one step launch (mpc.step | simulation.step | history row).
+ * history_dev as mpcb_session_closed_loop_dev; obs_history_dev NULL or double [nsteps,B,MPCB_MAX_OBSTACLES,6]: the
+ * rows `o.get()` returned at every step (the reference's `obstacles_positions`, :92,155).  Asynchronous, capturable. */
+int mpcb_session_scripted_loop_dev(mpcb_handle* h, int nsteps, double* history_dev, double* obs_history_dev, int flags,
+                                   void* stream);
+#define MPCB_F_SCRIPT 18    /* double [B,MPCB_MAX_OBSTACLES,8] xc, yc, theta, counter, direction, turning, speed, offset */
+#define MPCB_F_OBS 19       /* double [B,MPCB_MAX_OBSTACLES,6] last get() rows (when no obs_history_dev was given) */
+#define MPCB_F_NOBS 20      /* int    [B] scripted obstacles per ego */
+
 /* kernels launched by this handle so far (bench.py's gpu_launches) */
 long long mpcb_launch_count(const mpcb_handle* h);
 

@@ -39,10 +39,11 @@ EXPORTS = [
     "mpcb_session_closed_loop_dev", "mpcb_session_device_ptr", "mpcb_session_field_bytes",
     "mpcb_session_fetch_host", "mpcb_session_store_host",
     "mpcb_coupling", "mpcb_coupling_host", "mpcb_session_multi_agent_dev",
+    "mpcb_session_set_scripted_host", "mpcb_session_scripted_loop_dev",
 ]
 
 F_STATE, F_OA, F_OD, F_TRAJ, F_XREF, F_DI_AI, F_XDEV, F_TARGET, F_WARM, F_STATUS, F_ITERS, F_DONE, F_NCOURSE, \
-    F_ROUTE, F_GOAL, F_AGENT_IDX, F_COLLIDED, F_COLL_IDX = range(18)
+    F_ROUTE, F_GOAL, F_AGENT_IDX, F_COLLIDED, F_COLL_IDX, F_SCRIPT, F_OBS, F_NOBS = range(21)
 MAX_OBSTACLES = 8
 
 
@@ -123,6 +124,10 @@ def lib():
     L.mpcb_coupling_host.restype = C.c_int
     L.mpcb_session_multi_agent_dev.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, vp]
     L.mpcb_session_multi_agent_dev.restype = C.c_int
+    L.mpcb_session_set_scripted_host.argtypes = [vp, vp, vp]
+    L.mpcb_session_set_scripted_host.restype = C.c_int
+    L.mpcb_session_scripted_loop_dev.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]
+    L.mpcb_session_scripted_loop_dev.restype = C.c_int
     L.mpcb_launch_count.argtypes = [vp]
     L.mpcb_launch_count.restype = C.c_longlong
     L.mpcb_measure_fp64_peak.argtypes = [C.c_int, dp]

@@ -52,8 +52,10 @@ struct mpcb_handle {
         double *state = nullptr, *L = nullptr, *oa = nullptr, *od = nullptr, *traj = nullptr, *xref = nullptr,
                *di_ai = nullptr, *xdev = nullptr, *goal = nullptr;
         int *route = nullptr, *ncourse = nullptr, *target = nullptr, *warm = nullptr, *status = nullptr,
-            *iters = nullptr, *done = nullptr, *agent_idx = nullptr, *collided = nullptr, *coll_idx = nullptr;
-        bool hasL = false;
+            *iters = nullptr, *done = nullptr, *agent_idx = nullptr, *collided = nullptr, *coll_idx = nullptr,
+            *n_script = nullptr;
+        double *script = nullptr, *obs = nullptr;      // scripted cross traffic [B,8,8] and its last get() rows [B,8,6]
+        bool hasL = false, has_script = false;
         size_t pin_state = 0, pin_diai = 0, pin_status = 0, pin_total = 0;
     } ses;
 };
@@ -491,7 +493,8 @@ int session_alloc(mpcb_handle* h) {
                  o_traj = put(8 * 4 * (T + 1) * B), o_xref = put(8 * 4 * (T + 1) * B), o_diai = put(8 * 2 * B),
                  o_xdev = put(8 * B), o_goal = put(8 * 2 * B), o_route = put(4 * B), o_nc = put(4 * B),
                  o_tgt = put(4 * B), o_warm = put(4 * B), o_status = put(4 * B), o_iters = put(4 * B),
-                 o_done = put(4 * B), o_aidx = put(4 * B), o_coll = put(4 * B), o_cidx = put(4 * B);
+                 o_done = put(4 * B), o_aidx = put(4 * B), o_coll = put(4 * B), o_cidx = put(4 * B),
+                 o_nscr = put(4 * B), o_script = put(8 * 8 * MPCB_CP_MAX_OBS * B), o_obs = put(8 * 6 * MPCB_CP_MAX_OBS * B);
     CUDA_TRY(h, cudaMalloc(&s.slab, o));
     CUDA_TRY(h, cudaMemset(s.slab, 0, o));
     char* d = s.slab;
@@ -501,6 +504,7 @@ int session_alloc(mpcb_handle* h) {
     s.ncourse = (int*)(d + o_nc); s.target = (int*)(d + o_tgt); s.warm = (int*)(d + o_warm);
     s.status = (int*)(d + o_status); s.iters = (int*)(d + o_iters); s.done = (int*)(d + o_done);
     s.agent_idx = (int*)(d + o_aidx); s.collided = (int*)(d + o_coll); s.coll_idx = (int*)(d + o_cidx);
+    s.n_script = (int*)(d + o_nscr); s.script = (double*)(d + o_script); s.obs = (double*)(d + o_obs);
     o = 0;
     s.pin_state = put(8 * 4 * B); s.pin_diai = put(8 * 2 * B); s.pin_status = put(4 * B);
     s.pin_total = o;
@@ -539,7 +543,7 @@ int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* 
         if (nc[b] < 1 || nc[b] > h->len_host[r]) { h->err = "mpcb_session_begin: ncourse out of range"; return MPCB_EINVAL; }
         goal[2 * b] = h->goal_host[2 * r]; goal[2 * b + 1] = h->goal_host[2 * r + 1];
     }
-    s.B = B; s.hasL = L_host != nullptr;
+    s.B = B; s.hasL = L_host != nullptr; s.has_script = false;
     cudaStream_t st = h->own_stream;
     CUDA_TRY(h, cudaMemcpyAsync(s.route, route_host, 4 * (size_t)B, cudaMemcpyHostToDevice, st));
     CUDA_TRY(h, cudaMemcpyAsync(s.ncourse, nc.data(), 4 * (size_t)B, cudaMemcpyHostToDevice, st));
@@ -617,6 +621,7 @@ void* mpcb_session_device_ptr(mpcb_handle* h, int what) {
         case MPCB_F_STATUS: return s.status; case MPCB_F_ITERS: return s.iters;   case MPCB_F_DONE: return s.done;
         case MPCB_F_NCOURSE: return s.ncourse; case MPCB_F_ROUTE: return s.route; case MPCB_F_GOAL: return s.goal;
         case MPCB_F_AGENT_IDX: return s.agent_idx; case MPCB_F_COLLIDED: return s.collided; case MPCB_F_COLL_IDX: return s.coll_idx;
+        case MPCB_F_SCRIPT: return s.script; case MPCB_F_OBS: return s.obs; case MPCB_F_NOBS: return s.n_script;
         default: return nullptr;
     }
 }
@@ -628,7 +633,10 @@ static size_t field_bytes(const mpcb_handle* h, int what) {
         case MPCB_F_TRAJ: case MPCB_F_XREF: return 32 * (T + 1) * B;
         case MPCB_F_DI_AI: case MPCB_F_GOAL: return 16 * B;  case MPCB_F_XDEV: return 8 * B;
         case MPCB_F_TARGET: case MPCB_F_WARM: case MPCB_F_STATUS: case MPCB_F_ITERS: case MPCB_F_DONE:
-        case MPCB_F_NCOURSE: case MPCB_F_ROUTE: case MPCB_F_AGENT_IDX: case MPCB_F_COLLIDED: case MPCB_F_COLL_IDX: return 4 * B;
+        case MPCB_F_NCOURSE: case MPCB_F_ROUTE: case MPCB_F_AGENT_IDX: case MPCB_F_COLLIDED: case MPCB_F_COLL_IDX:
+        case MPCB_F_NOBS: return 4 * B;
+        case MPCB_F_SCRIPT: return 8 * 8 * MPCB_CP_MAX_OBS * B;
+        case MPCB_F_OBS: return 8 * 6 * MPCB_CP_MAX_OBS * B;
         default: return 0;
     }
 }
@@ -754,14 +762,12 @@ int mpcb_coupling_host(mpcb_handle* h, int B, const double* state, const int* ro
     return rc;
 }
 
-int mpcb_session_multi_agent_dev(mpcb_handle* h, int nsteps, int vehicles_per_scenario, double* history_dev, int flags,
-                                 void* stream) {
-    if (!h || h->ses.B <= 0 || nsteps <= 0 || vehicles_per_scenario < 1) { if (h) h->err = "mpcb_session_multi_agent_dev: bad arguments / no session"; return MPCB_EINVAL; }
+// Coupled closed loop shared by the multi-agent sweep (obstacles = the other egos of a scenario) and the scripted
+// cross-traffic sweep (obstacles = MovingObstacleTIntersection scripts stepped inside the coupling kernel).
+static int coupled_loop(mpcb_handle* h, int nsteps, int vehicles_per_scenario, bool scripted, double* history_dev,
+                        double* obs_history_dev, int flags, cudaStream_t stream) {
     auto& s = h->ses;
-    h->last_stream = (cudaStream_t)stream; h->last_stream_set = true;
-    if (vehicles_per_scenario > MPCB_CP_MAX_OBS + 1 || s.B % vehicles_per_scenario != 0) {
-        h->err = "mpcb_session_multi_agent_dev: vehicles_per_scenario must be 1..9 and divide B"; return MPCB_EINVAL;
-    }
+    h->last_stream = stream; h->last_stream_set = true;
     StepParams p = session_params(h);
     p.done = s.done; p.goal = s.goal; p.state_out = s.state; p.fuse_goal = 0; p.fuse_plant = 1;
     for (int k = 0; k < nsteps; ++k) {
@@ -774,13 +780,64 @@ int mpcb_session_multi_agent_dev(mpcb_handle* h, int nsteps, int vehicles_per_sc
         cp.done = s.done; cp.agent_idx = s.agent_idx; cp.ncourse = s.ncourse; cp.collided = s.collided; cp.coll_idx = s.coll_idx;
         cp.goal = s.goal; cp.target_ind = s.target; cp.fuse_goal = (flags & MPCB_CL_NO_GOAL_TEST) ? 0 : 1;
         cp.goal_dis = h->cfg.goal_dis; cp.stop_speed = h->cfg.stop_speed;
-        int rc = launch_coupling(h, cp, (cudaStream_t)stream);
+        if (scripted) {
+            cp.script = s.script; cp.n_obs = s.n_script;
+            cp.obs_out = obs_history_dev ? obs_history_dev + (size_t)k * 6 * MPCB_CP_MAX_OBS * s.B : s.obs;
+        }
+        int rc = launch_coupling(h, cp, stream);
         if (rc != MPCB_OK) return rc;
         p.history = history_dev ? history_dev + (size_t)k * 8 * s.B : nullptr;
-        rc = dispatch_step(h, p, (cudaStream_t)stream);
+        rc = dispatch_step(h, p, stream);
         if (rc != MPCB_OK) return rc;
     }
     return MPCB_OK;
+}
+
+int mpcb_session_multi_agent_dev(mpcb_handle* h, int nsteps, int vehicles_per_scenario, double* history_dev, int flags,
+                                 void* stream) {
+    if (!h || h->ses.B <= 0 || nsteps <= 0 || vehicles_per_scenario < 1) { if (h) h->err = "mpcb_session_multi_agent_dev: bad arguments / no session"; return MPCB_EINVAL; }
+    if (vehicles_per_scenario > MPCB_CP_MAX_OBS + 1 || h->ses.B % vehicles_per_scenario != 0) {
+        h->err = "mpcb_session_multi_agent_dev: vehicles_per_scenario must be 1..9 and divide B"; return MPCB_EINVAL;
+    }
+    return coupled_loop(h, nsteps, vehicles_per_scenario, false, history_dev, nullptr, flags, (cudaStream_t)stream);
+}
+
+int mpcb_session_set_scripted_host(mpcb_handle* h, const double* script_host, const int* n_obs_host) {
+    if (!h || h->ses.B <= 0 || !script_host || !n_obs_host) { if (h) h->err = "mpcb_session_set_scripted_host: bad arguments / no session"; return MPCB_EINVAL; }
+    auto& s = h->ses;
+    const size_t B = (size_t)s.B;
+    std::vector<double> st(B * MPCB_CP_MAX_OBS * 8, 0.0);
+    for (size_t b = 0; b < B; ++b) {
+        if (n_obs_host[b] < 0 || n_obs_host[b] > MPCB_CP_MAX_OBS) { h->err = "mpcb_session_set_scripted_host: n_obs out of range"; return MPCB_EINVAL; }
+        for (int o = 0; o < n_obs_host[b]; ++o) {
+            const double* in = script_host + (b * MPCB_CP_MAX_OBS + o) * 4;      // direction, turning, speed, offset
+            double* out = &st[(b * MPCB_CP_MAX_OBS + o) * 8];
+            const bool right = in[0] >= 0.0;                                       // moving_obstacles.py:177
+            out[0] = right ? -30.0 : 30.0;                                         // :186-196
+            out[1] = right ? -3.0 : 3.0;
+            out[2] = right ? 0.0 : 3.141592653589793;
+            out[3] = 0.0;                                                          // counter (:185)
+            out[4] = right ? 1.0 : -1.0;
+            out[5] = in[1] != 0.0 ? 1.0 : 0.0;
+            out[6] = in[2];
+            out[7] = (in[3] > 0.0) ? in[3] : 0.0;                                  // offset None unless > 0 (:181)
+        }
+    }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
+    CUDA_TRY(h, cudaMemcpyAsync(s.script, st.data(), 8 * st.size(), cudaMemcpyHostToDevice, h->own_stream));
+    CUDA_TRY(h, cudaMemcpyAsync(s.n_script, n_obs_host, 4 * B, cudaMemcpyHostToDevice, h->own_stream));
+    CUDA_TRY(h, cudaMemsetAsync(s.obs, 0, 8 * 6 * MPCB_CP_MAX_OBS * B, h->own_stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
+    s.has_script = true;
+    return MPCB_OK;
+}
+
+int mpcb_session_scripted_loop_dev(mpcb_handle* h, int nsteps, double* history_dev, double* obs_history_dev, int flags,
+                                   void* stream) {
+    if (!h || h->ses.B <= 0 || nsteps <= 0) { if (h) h->err = "mpcb_session_scripted_loop_dev: bad arguments / no session"; return MPCB_EINVAL; }
+    if (!h->ses.has_script) { h->err = "mpcb_session_scripted_loop_dev: call mpcb_session_set_scripted_host first"; return MPCB_EINVAL; }
+    return coupled_loop(h, nsteps, 0, true, history_dev, obs_history_dev, flags, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -27,6 +27,10 @@ struct CouplingParams {
     const int* route;            // [B]
     const double* obs;           // [B, MPCB_CP_MAX_OBS, 6] x y v yaw a steer (MovingObstacle*.get()), or null
     const int* n_obs;            // [B] or null
+    double* script;              // [B, MPCB_CP_MAX_OBS, 8] io or null: scripted cross traffic (MovingObstacleTIntersection,
+                                 //   main/lib/moving_obstacles.py:165-231) stepped HERE, once per launch: xc, yc, theta,
+                                 //   counter | direction, turning, speed, offset (<= 0: none).  Takes the place of `obs`.
+    double* obs_out;             // [B, MPCB_CP_MAX_OBS, 6] or null: what MovingObstacleTIntersection.get() returned this step
     int* done;                   // [B] or null: finished egos keep their cut (and still act as obstacles)
     const double* goal;          // [B,2], target_ind [B]: with fuse_goal the loop-head test MPC.is_goal
     const int* target_ind;       //   (mpc_intersection.py:97, mpc.py:310-326) runs here, against the PREVIOUS cut
@@ -160,9 +164,35 @@ __global__ void __launch_bounds__(WARPS * 32) coupling_kernel(const CouplingPara
             const int other = s0 + (lane < me ? lane : lane + 1);
             ox = p.state[4 * other]; oy = p.state[4 * other + 1]; oyaw = p.state[4 * other + 2]; ov = p.state[4 * other + 3];
             oa = 0.0; ost = 0.0;
+        } else if (p.script) {
+            // scripted obstacle: get() (moving_obstacles.py:230-232) feeds this step's prediction, then step() (:225-228)
+            // moves the model on -- the order of the reference loop (mpc_intersection.py:118-121 before :154-156)
+            double* s8 = p.script + ((size_t)b * MPCB_CP_MAX_OBS + lane) * 8;
+            const double xc = s8[0], yc = s8[1], th = s8[2], cnt = s8[3], dir = s8[4], turning = s8[5], spd = s8[6], off = s8[7];
+            // forward_velocity (:218-223): `offset is None or counter > offset / dt`
+            const double fv = (!(off > 0.0) || cnt > __ddiv_rn(off, p.dt)) ? spd : 0.0;
+            // steering_angle (:203-216): x_turn = -10 / 12 (:190,195); -np.pi / 2 and 3 * np.pi / 2 in the reference's operation order
+            const double kPi = 3.141592653589793;
+            double st = 0.0;
+            if (turning != 0.0) {
+                if (dir > 0.0) { if (xc >= -10.0 && th > __ddiv_rn(-kPi, 2.0)) st = -0.38; }
+                else { if (xc <= 12.0 && th < __ddiv_rn(__dmul_rn(3.0, kPi), 2.0)) st = 0.19; }
+            }
+            ox = xc; oy = yc; ov = fv; oyaw = th; oa = 0.0; ost = st;
+            // Bicycle.step(v, delta) (main/bicycle/main.py:28-41), unfused like numpy
+            double sn, cs;
+            sincos(th, &sn, &cs);
+            s8[0] = __dadd_rn(xc, __dmul_rn(__dmul_rn(fv, cs), p.dt));
+            s8[1] = __dadd_rn(yc, __dmul_rn(__dmul_rn(fv, sn), p.dt));
+            s8[2] = __dadd_rn(th, __dmul_rn(__dmul_rn(__ddiv_rn(fv, p.wheelbase), tan(st)), p.dt));
+            s8[3] = cnt + 1.0;
         } else {
             const double* o6 = p.obs + ((size_t)b * MPCB_CP_MAX_OBS + lane) * 6;
             ox = o6[0]; oy = o6[1]; ov = o6[2]; oyaw = o6[3]; oa = o6[4]; ost = o6[5];
+        }
+        if (p.obs_out) {
+            double* w6 = p.obs_out + ((size_t)b * MPCB_CP_MAX_OBS + lane) * 6;
+            w6[0] = ox; w6[1] = oy; w6[2] = ov; w6[3] = oyaw; w6[4] = oa; w6[5] = ost;
         }
         // pass A (sequential per obstacle): the yaw and speed sequences.  x, y of frame f use the OLD v / yaw, the
         // yaw update uses the NEW v (moving_obstacles_prediction.py:33-40); yaw_0..yaw_nf go to ocx[o][0][f]

@@ -33,6 +33,9 @@ _FIELDS = {
     "agent_idx": (_lib.F_AGENT_IDX, np.int32, lambda T: ()),
     "collided": (_lib.F_COLLIDED, np.int32, lambda T: ()),
     "coll_idx": (_lib.F_COLL_IDX, np.int32, lambda T: ()),
+    "script": (_lib.F_SCRIPT, np.float64, lambda T: (_lib.MAX_OBSTACLES, 8)),
+    "obstacles": (_lib.F_OBS, np.float64, lambda T: (_lib.MAX_OBSTACLES, 6)),
+    "n_obstacles": (_lib.F_NOBS, np.int32, lambda T: ()),
 }
 
 
@@ -112,6 +115,37 @@ class MpcSession:
         _lib.check(self._lib.mpcb_session_multi_agent_dev(
             self._h, int(nsteps), int(vehicles_per_scenario), C.c_void_p(history_ptr) if history_ptr else None,
             0 if goal_test else 1, C.c_void_p(cuda_stream)), self._h, "mpcb_session_multi_agent_dev")
+
+    def set_scripted_obstacles(self, scripts):
+        """scripts: per ego a list of (direction, turning, speed, offset) tuples -- the constructor arguments of the
+        reference's `MovingObstacleTIntersection` (main/lib/moving_obstacles.py:165-196; offset None or <= 0 = starts
+        at once) -- or a ready [B, MAX_OBSTACLES, 4] array with n_obs inferred from NaN rows."""
+        B, M = self.B, _lib.MAX_OBSTACLES
+        arr = np.zeros((B, M, 4))
+        n = np.zeros(B, np.int32)
+        if isinstance(scripts, np.ndarray):
+            assert scripts.shape == (B, M, 4)
+            n[:] = (~np.isnan(scripts[:, :, 0])).sum(axis=1)
+            arr[:] = np.nan_to_num(scripts)
+        else:
+            assert len(scripts) == B
+            for b, lst in enumerate(scripts):
+                assert len(lst) <= M
+                n[b] = len(lst)
+                for o, (direction, turning, speed, offset) in enumerate(lst):
+                    arr[b, o] = (direction, 1.0 if turning else 0.0, speed, 0.0 if offset is None else offset)
+        _lib.check(self._lib.mpcb_session_set_scripted_host(self._h, _p(arr), _p(n)), self._h,
+                   "mpcb_session_set_scripted_host")
+
+    def scripted_loop_dev(self, nsteps: int, history_ptr: int = 0, obs_history_ptr: int = 0, cuda_stream: int = 0,
+                          goal_test: bool = True):
+        """The reference's whole loop body with scripted cross traffic (main/scenarios/mpc_intersection.py:95-159) on
+        the device: nsteps x (is_goal | obstacle get()/step() | coupling | MPC.step | Simulation.step), two launches
+        per control step, no host round trip.  obs_history_ptr: device float64 [nsteps,B,MAX_OBSTACLES,6] or 0."""
+        _lib.check(self._lib.mpcb_session_scripted_loop_dev(
+            self._h, int(nsteps), C.c_void_p(history_ptr) if history_ptr else None,
+            C.c_void_p(obs_history_ptr) if obs_history_ptr else None, 0 if goal_test else 1, C.c_void_p(cuda_stream)),
+            self._h, "mpcb_session_scripted_loop_dev")
 
     def coupling(self, state, route, agent_idx, ncourse, obs=None, n_obs=None, vehicles_per_scenario=0):
         """Row A9 with host buffers (mpcb_coupling_host): the coupling part of the reference loop body

@@ -192,3 +192,85 @@ def multi_agent_closed_loop(routes_smooth, route, state0, target0, nsteps, T, of
             hist[k, j] = (*new_state[j], di, ai_, dev, m.status)
         state = new_state
     return hist, done, nclog
+
+
+class ScriptedObstacle:
+    """main/lib/moving_obstacles.py:165-231 (`MovingObstacleTIntersection`) with the Bicycle model of
+    main/bicycle/main.py:28-41: a scripted car crossing the junction, independent of the ego."""
+
+    def __init__(self, direction, turning, speed, offset, L, dt):
+        self.direction = 1 if direction >= 0 else -1                      # :177
+        self.turning, self.speed, self.L, self.dt = bool(turning), speed, L, dt
+        self.offset = None if offset is None else offset if offset > 0 else None     # :181
+        self.counter = 0
+        if self.direction == 1:                                           # :186-196
+            self.xc, self.yc, self.theta, self.x_turn = -30, -3, 0, -10
+        else:
+            self.xc, self.yc, self.theta, self.x_turn = 30, 3, np.pi, 12
+
+    @property
+    def steering_angle(self):                                            # :201-216
+        if self.turning is not True:
+            return 0.
+        if self.direction == 1:
+            if self.xc >= self.x_turn and self.theta > (-np.pi / 2):
+                return -0.38
+        else:
+            if self.xc <= self.x_turn and self.theta < (3 * np.pi / 2):
+                return 0.19
+        return 0.
+
+    @property
+    def forward_velocity(self):                                          # :218-224
+        if self.offset is None or self.counter > (self.offset / self.dt):
+            return self.speed
+        return 0
+
+    def step(self):                                                      # :225-228, bicycle/main.py:34-41
+        delta, v = self.steering_angle, self.forward_velocity
+        xd = v * np.cos(self.theta)
+        yd = v * np.sin(self.theta)
+        td = (v / self.L) * np.tan(delta)
+        self.xc += xd * self.dt
+        self.yc += yd * self.dt
+        self.theta += td * self.dt
+        self.counter += 1
+
+    def get(self):                                                       # :230-232
+        return self.xc, self.yc, self.forward_velocity, self.theta, 0.0, self.steering_angle
+
+
+def scripted_closed_loop(full, state0, scripts, nsteps, T, offs, radius, L, dt=0.2, target0=0):
+    """The loop body of main/scenarios/mpc_intersection.py:95-159 for one ego with scripted cross traffic
+    (`scripts`: (direction, turning, speed, offset) tuples).  Returns history [nsteps, 8] (x, y, yaw, v after the plant
+    step, delta, a, xref_deviation, status; NaN rows once the goal is reached), the cut log [nsteps] (0 once done), the
+    obstacle rows [nsteps, n_obs, 6] that `get()` returned, and the number of steps run."""
+    import mpc_oracle as mo
+    cfg = mo.Cfg.from_dict({"T": T})
+    m = mo.OracleMPC(full[:, 0].copy(), full[:, 1].copy(), full[:, 2].copy(),
+                     float(np.linalg.norm(full[0, :2] - full[1, :2])), L, dt, cfg)
+    m.target_ind = int(target0)
+    obstacles = [ScriptedObstacle(*s, L, dt) for s in scripts]
+    state = np.array(state0, float)
+    agent_idx, ncourse = 0, 0
+    hist = np.full((nsteps, 8), np.nan)
+    nclog = np.zeros(nsteps, int)
+    obslog = np.full((nsteps, len(obstacles), 6), np.nan)
+    for k in range(nsteps):
+        if m.is_goal(state):                                             # :97
+            return hist, nclog, obslog, k
+        agent_idx = agent_index_update(full, agent_idx, ncourse, state[0], state[1])      # :103-105
+        assert agent_idx >= 0
+        rows = [o.get() for o in obstacles]                              # :118-121
+        obslog[k] = np.array(rows, float).reshape(len(obstacles), 6)
+        c = coupling_step(full, agent_idx, state[3], rows, offs, radius, L, dt)
+        ncourse = c["cutoff_idx"]
+        nclog[k] = ncourse
+        m.set_trajectory_fromarray(full[:ncourse])                       # :139
+        di, ai = m.step(state)                                           # :142
+        for o in obstacles:                                              # :154-156
+            o.step()
+        dev = m.get_current_xref_deviation() if (m.ox is not None and m.target_ind < len(m.cx)) else np.nan
+        state = np.array(mo.plant_step(state[0], state[1], state[2], state[3], ai, di, L, dt))   # :159
+        hist[k] = (*state, di, ai, dev, m.status)
+    return hist, nclog, obslog, nsteps

@@ -54,3 +54,38 @@ def test_no_obstacles_and_degenerate_paths(routes_smooth):
     assert out["collided"] == 0 and out["cutoff_idx"] == len(full)
     last = co.coupling_step(full, len(full) - 1, 0.0, np.array([[full[-1, 0], full[-1, 1], 0, 0, 0, 0.0]]), offs, radius, 2.86)
     assert last["n_res"] == 1 and last["collided"] == 1 and last["cutoff_idx"] == len(full)   # max(idx + 1, j - 72)
+
+
+REF_SCRIPTS = [(1, False, 25 / 3.6, 2.), (-1, True, 25 / 3.6, 4.)]        # main/scenarios/mpc_intersection.py:41-44
+
+
+@pytest.mark.parametrize("T", [13, 20])
+def test_scripted_obstacle_model_is_bit_exact(T):
+    """oracle ScriptedObstacle vs every `o.get()` row the reference's MovingObstacleTIntersection objects returned."""
+    g = golden(f"closed_loop_T{T}.npz")
+    sel = np.flatnonzero(g["loop"] == 12)
+    obs = [co.ScriptedObstacle(*s, 2.86, 0.2) for s in REF_SCRIPTS]
+    for k in sel:
+        assert np.array_equal(np.array([o.get() for o in obs], float), g["obs"][k])
+        for o in obs:
+            o.step()
+    assert g["obs"][sel][:, 1, 5].max() == 0.19 and g["obs"][sel][0, :, 2].max() == 0.0      # turning seen, both start parked
+
+
+def test_scripted_closed_loop_oracle_reproduces_reference_loop(routes_smooth):
+    """The composed oracle loop (ScriptedObstacle + coupling_step + OracleMPC + plant) against the reference's own
+    recorded loop with two scripted cars: steps to goal, every cut length and obstacle row bit-exact; states to 1e-6
+    over the first 45 steps (the route is a left turn: see DESIGN.md "closed-loop sensitivity")."""
+    T = 13
+    g = golden(f"closed_loop_T{T}.npz")
+    sel = np.flatnonzero(g["loop"] == 12)
+    offs, radius = co.circle_offsets(*CARS[0])
+    full = routes_smooth[int(g["route"][sel[0]])]
+    hist, nclog, obslog, n = co.scripted_closed_loop(full, g["state"][sel[0]], REF_SCRIPTS, len(sel) + 3, T, offs, radius, 2.86)
+    assert n == len(sel)
+    assert np.array_equal(nclog[:n], g["ncourse"][sel])
+    assert np.array_equal(obslog[:n], g["obs"][sel])
+    off = g["history_off"]
+    ref = g["history"][off[12]:off[13]][1:n + 1]
+    assert np.abs(hist[:45, :4] - ref[:45, :4]).max() < 1e-6
+    assert np.abs(hist[:n, :2] - ref[:, :2]).max() < 1e-3

@@ -144,3 +144,101 @@ def test_multi_agent_closed_loop_matches_oracle(routes_smooth):
     assert cuts > 20, "the scenarios must actually interact"
     print(f"multi-agent: {S}x{V} vehicles, {K} steps, {cuts} path cuts, max|dstate|={worst:.2e}")
     assert worst < 1e-6
+
+
+REF_SCRIPTS = [(1, False, 25 / 3.6, 2.), (-1, True, 25 / 3.6, 4.)]        # main/scenarios/mpc_intersection.py:41-44
+
+
+@pytest.mark.parametrize("T", [13, 20])
+def test_scripted_loop_on_device_matches_reference(T, routes_smooth):
+    """the reference's whole loop body WITH its two scripted cars (mpc_intersection.py:95-159) run on the
+    device without host round trips (mpcb_session_scripted_loop_dev, two launches per control step), against the
+    loop the unmodified reference recorded: steps to goal and every cut length bit-exact, the obstacle rows `o.get()`
+    returned to 1e-12, positions within 1e-3 m over the rollout (1e-6 over the first 45 steps: left-turn route)."""
+    import torch
+    from mpc_for_av_at_intersection_b200 import _lib
+    g = golden(f"closed_loop_T{T}.npz")
+    sel = np.flatnonzero(g["loop"] == 12)
+    n = len(sel)
+    ses, cfg = _session(0, T)
+    B = 3                                                   # replicas: every ego owns its copy of the cross traffic
+    ses.begin(np.full(B, int(g["route"][sel[0]]), np.int32))
+    ses.store("state", np.repeat(g["state"][sel[0]][None], B, 0))
+    ses.set_scripted_obstacles([REF_SCRIPTS] * B)
+    K = n + 3
+    H = torch.full((K, B, 8), float("nan"), dtype=torch.float64, device="cuda")
+    OH = torch.full((K, B, _lib.MAX_OBSTACLES, 6), float("nan"), dtype=torch.float64, device="cuda")
+    before = ses.launches
+    # step by step for the cut log, then compare the histories
+    nclog = np.zeros((K, B), int)
+    for k in range(K):
+        ses.scripted_loop_dev(1, H[k].data_ptr(), OH[k].data_ptr())
+        nclog[k] = ses.fetch("ncourse")
+    torch.cuda.synchronize()
+    assert ses.launches - before == 2 * K
+    H, OH = H.cpu().numpy(), OH.cpu().numpy()
+    assert np.array_equal(ses.fetch("done"), np.ones(B, np.int32))
+    off = g["history_off"]
+    ref = g["history"][off[12]:off[13]][1:n + 1]
+    for b in range(B):
+        valid = ~np.isnan(H[:, b, 0])
+        assert valid.sum() == n and valid[:n].all(), (valid.sum(), n)
+        assert np.array_equal(nclog[:n, b], g["ncourse"][sel])
+        assert np.abs(OH[:n, b, :2] - g["obs"][sel]).max() < 1e-12
+        ep = np.abs(H[:n, b, :2] - ref[:, :2]).max(axis=1)
+        assert ep.max() < 1e-3 and ep[:45].max() < 1e-6, (ep.max(), ep[:45].max())
+        assert np.abs(H[:45, b, 4:6] - ref[:45, 4:6]).max() < 1e-6
+    print(f"T={T}: scripted loop on device, {n} steps, cuts bit-exact, max|dpos|={np.abs(H[:n, :, :2] - ref[None, :, :2].transpose(1, 0, 2)).max():.2e}")
+
+
+def test_scripted_loop_random_scripts_vs_oracle_and_graph(routes_smooth):
+    """Randomised cross traffic (direction, turning, speed, start offset; 0-3 cars per ego) on all 12 routes: the device
+    loop captured into ONE CUDA graph (30 control steps = 60 kernel nodes, replayed by a single launch) against the
+    composed numpy oracle -- cut lengths bit-exact every step, states within 1e-6."""
+    import torch
+    T, K = 20, 30
+    rng = np.random.default_rng(5)
+    ses, cfg = _session(0, T)
+    B = 24
+    route = (np.arange(B) % 12).astype(np.int32)
+    scripts = []
+    for b in range(B):
+        scripts.append([(int(rng.choice([-1, 1])), bool(rng.integers(0, 2)), float(rng.uniform(3, 9)),
+                         float(rng.choice([0.0, rng.uniform(0.2, 3.0)]))) for _ in range(int(rng.integers(0, 4)))])
+    state0 = np.stack([np.array([routes_smooth[r][0, 0], routes_smooth[r][0, 1], routes_smooth[r][0, 2], rng.uniform(0, 4)])
+                       for r in route])
+    ses.begin(route)
+    ses.store("state", state0)
+    ses.set_scripted_obstacles(scripts)
+    H = torch.full((K, B, 8), float("nan"), dtype=torch.float64, device="cuda")
+    NC = torch.zeros((K, B), dtype=torch.int32, device="cuda")
+    nc_view = torch.as_tensor(ses.device_view("ncourse"), device="cuda")
+    stream = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    # warm-up launch outside the capture (function attributes are set on first use), then reset the session
+    ses.scripted_loop_dev(1)
+    torch.cuda.synchronize()
+    ses.begin(route)
+    ses.store("state", state0)
+    ses.set_scripted_obstacles(scripts)
+    with torch.cuda.graph(graph, stream=stream):
+        for k in range(K):
+            ses.scripted_loop_dev(1, H[k].data_ptr(), 0, torch.cuda.current_stream().cuda_stream)
+            NC[k].copy_(nc_view)
+    before = ses.launches
+    graph.replay()
+    torch.cuda.synchronize()
+    assert ses.launches == before, "the replay is one graph launch: no per-kernel host launches"
+    H, NC = H.cpu().numpy(), NC.cpu().numpy()
+    offs, radius = co.circle_offsets(*CARS[0])
+    cuts, worst = 0, 0.0
+    for b in range(B):
+        full = routes_smooth[route[b]]
+        hist, nclog, _, n = co.scripted_closed_loop(full, state0[b], scripts[b], K, T, offs, radius, 2.86)
+        assert n == K
+        assert np.array_equal(NC[:, b], nclog), (b, NC[:, b], nclog)
+        cuts += int((nclog < len(full)).sum())
+        worst = max(worst, np.abs(H[:, b, :6] - hist[:, :6]).max())
+    assert cuts > 30, "the cross traffic must actually cut paths"
+    print(f"scripted loop in one CUDA graph: {B} egos x {K} steps, {cuts} cut steps, max|dstate,u|={worst:.2e}")
+    assert worst < 1e-6
