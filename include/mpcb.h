@@ -76,6 +76,9 @@ typedef struct mpcb_config {
     double car_length;     /* wheelbase + 0.64 = 3.5 / 4.84 s                                        */
     double coupling_horizon; /* TIME_HORIZON = 7.0 s -> 35 predicted obstacle frames at dt = 0.2       */
     int frame_window;      /* FRAME_WINDOW = 20: obstacle trajectories are time-shifted by -20..+20 frames */
+    /* controller variant main/lib/mpc_with_speed.py: speed reference xref[2,t] = cv[idx_t] (:104) with cv = ref_speed
+     * (its MAX_SPEED = 25/3.6, :36,280) and 0 from the per-problem cutoff index on (:281-282).  0 = main/lib/mpc.py */
+    double ref_speed;
 } mpcb_config;
 
 typedef struct mpcb_handle mpcb_handle;
@@ -169,6 +172,16 @@ int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* 
                        const double* L_host, const int* target_ind_host);
 /* replaces: MPC.set_trajectory_fromarray(full[:cutoff]) (main/lib/mpc.py:275-278) for the batch */
 int mpcb_session_set_ncourse_host(mpcb_handle* h, const int* ncourse_host);
+/* replaces: main/lib/mpc_sensitivity.py:150-158, which re-reads w_perp, w_para, R, Rd, Q_v_yaw, Qf from its JSON on
+ * every solve so that main/scenarios/mpc_sensitivity_analysis_comulative.py:152-157 can sweep them: here every problem
+ * of the batch carries its own row, so a whole sweep (5 values x 6 parameters x routes) is ONE batch.
+ * weights_host [B,12]: w_perp, w_para, R[0], R[1], Rd[0], Rd[1], Q_v_yaw[0], Q_v_yaw[1], Qf[0..3] (as in the file:
+ * the library scales Qf by T).  NULL = back to the handle's config.  Synchronous. */
+int mpcb_session_set_weights_host(mpcb_handle* h, const double* weights_host);
+/* replaces: the cutoff_idx argument of mpc_with_speed.MPC.set_trajectory_fromarray (main/lib/mpc_with_speed.py:276-282):
+ * the speed reference cv is cfg.ref_speed up to cutoff_idx_host[b] and 0 from there on (999 or any index past the
+ * course = no cut).  NULL = no cut anywhere.  Synchronous. */
+int mpcb_session_set_speed_cutoff_host(mpcb_handle* h, const int* cutoff_idx_host);
 /* replaces: `di, ai = mpc.step(state)` for the batch with HOST buffers: copies state[B,4] in, runs the
  * step kernel on the resident session, copies di_ai[B,2] (steer, accel) and status[B] (may be NULL)
  * out.  Synchronous. */

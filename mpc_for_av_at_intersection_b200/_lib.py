@@ -28,6 +28,7 @@ class mpcb_config(C.Structure):
         ("ipm_tol_d", C.c_double),
         ("car_width", C.c_double), ("car_length", C.c_double), ("coupling_horizon", C.c_double),
         ("frame_window", C.c_int),
+        ("ref_speed", C.c_double),
     ]
 
 
@@ -40,6 +41,7 @@ EXPORTS = [
     "mpcb_session_fetch_host", "mpcb_session_store_host",
     "mpcb_coupling", "mpcb_coupling_host", "mpcb_session_multi_agent_dev",
     "mpcb_session_set_scripted_host", "mpcb_session_scripted_loop_dev",
+    "mpcb_session_set_weights_host", "mpcb_session_set_speed_cutoff_host",
 ]
 
 F_STATE, F_OA, F_OD, F_TRAJ, F_XREF, F_DI_AI, F_XDEV, F_TARGET, F_WARM, F_STATUS, F_ITERS, F_DONE, F_NCOURSE, \
@@ -128,6 +130,10 @@ def lib():
     L.mpcb_session_set_scripted_host.restype = C.c_int
     L.mpcb_session_scripted_loop_dev.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]
     L.mpcb_session_scripted_loop_dev.restype = C.c_int
+    L.mpcb_session_set_weights_host.argtypes = [vp, vp]
+    L.mpcb_session_set_weights_host.restype = C.c_int
+    L.mpcb_session_set_speed_cutoff_host.argtypes = [vp, vp]
+    L.mpcb_session_set_speed_cutoff_host.restype = C.c_int
     L.mpcb_launch_count.argtypes = [vp]
     L.mpcb_launch_count.restype = C.c_longlong
     L.mpcb_measure_fp64_peak.argtypes = [C.c_int, dp]

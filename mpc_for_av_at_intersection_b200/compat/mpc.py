@@ -89,11 +89,19 @@ class MPC:
         self.ox = self.oy = self.oyaw = self.ov = None
         self.xref = None
         self.di, self.ai = 0.0, 0.0
-        self._cfg = MpcConfig.from_dict({k: v for k, v in _config.items()})
+        self._cfg = self._base_config()
         self._cfg.dt = float(dt)
         self._cfg.wheelbase = float(car_dimensions.distance_back_to_front_wheel)
         self._ses = None
         self._upload(np.stack([np.asarray(cx, float), np.asarray(cy, float), np.asarray(cyaw, float)], axis=1))
+
+    @staticmethod
+    def _base_config() -> MpcConfig:
+        """The module-level constants as a config object (the variants in compat/ override this)."""
+        return MpcConfig.from_dict({k: v for k, v in _config.items()})
+
+    def _after_new_session(self):
+        pass
 
     # ---- course handling ------------------------------------------------------------------------------------
     def _upload(self, course):
@@ -109,6 +117,7 @@ class MPC:
             for k, v in keep.items():
                 self._ses.store(k, v)
         self._ncourse = len(self._full)
+        self._after_new_session()
 
     def set_trajectory_fromarray(self, trajectory: np.ndarray):
         """main/lib/mpc.py:275-278: rebinds cx, cy, cyaw; target_ind, goal and the warm start are kept."""
@@ -149,7 +158,7 @@ class MPC:
         else:
             print("Error: Cannot solve mpc..", file=sys.stderr)      # mpc.py:204-206
             self.oa = self.odelta = self.ox = self.oy = self.oyaw = self.ov = None
-            self.ai = MAX_DECEL                                       # mpc.py:294-297: emergency braking, di kept
+            self.ai = self._cfg.MAX_DECEL                             # mpc.py:294-297: emergency braking, di kept
         self.status = status
         self.iters = int(ses.fetch("iters")[0])
         return self.di, self.ai
@@ -165,7 +174,7 @@ class MPC:
     def is_goal(self, state):
         """main/lib/mpc.py:310-326."""
         d = math.hypot(state.x - self.goal[0], state.y - self.goal[1])
-        isgoal = d <= GOAL_DIS
+        isgoal = d <= self._cfg.GOAL_DIS
         if abs(self.target_ind - len(self.cx)) >= 5:
             isgoal = False
-        return bool(isgoal and abs(state.v) <= STOP_SPEED)
+        return bool(isgoal and abs(state.v) <= self._cfg.STOP_SPEED)

@@ -41,6 +41,8 @@ class MpcConfig:
     car_length: float = 3.5
     coupling_horizon: float = 7.0
     frame_window: int = 20
+    # variant main/lib/mpc_with_speed.py: speed reference cv (its MAX_SPEED = 25/3.6); 0 = main/lib/mpc.py
+    ref_speed: float = 0.0
 
     @staticmethod
     def from_json(path=None, **overrides):
@@ -55,6 +57,22 @@ class MpcConfig:
         if unknown:
             raise KeyError(f"unknown mpc_config keys: {sorted(unknown)}")
         return MpcConfig(**d)
+
+    @staticmethod
+    def with_speed(**overrides):
+        """The constants main/lib/mpc_with_speed.py:16-36,161,165 hard-codes instead of reading the JSON."""
+        d = dict(T=13, w_perp=10.0, w_para=1.0, R=[0.01, 0.01], Rd=[0.01, 1.0], Q_v_yaw=[20.0, 0.5],
+                 Qf=[1.0, 1.0, 0.0, 0.5], GOAL_DIS=1.5, STOP_SPEED=0.5 / 3.6, MAX_TIME=13.0, MAX_ITER=1, DU_TH=0.1,
+                 MAX_DSTEER=30.0, MAX_ACCEL=2.0, MAX_DECEL=-5.0, ref_speed=25 / 3.6)
+        return MpcConfig.from_dict({**d, **overrides})
+
+    WEIGHT_KEYS = ("w_perp", "w_para", "R", "Rd", "Q_v_yaw", "Qf")
+
+    def weight_row(self, **overrides):
+        """[12] row for MpcSession.set_weights: w_perp, w_para, R[2], Rd[2], Q_v_yaw[2], Qf[4] (file units)."""
+        g = lambda k: overrides.get(k, getattr(self, k))
+        return [float(g("w_perp")), float(g("w_para")), *map(float, g("R")), *map(float, g("Rd")),
+                *map(float, g("Q_v_yaw")), *map(float, g("Qf"))]
 
     def to_c(self):
         c = _lib.mpcb_config()
@@ -74,4 +92,5 @@ class MpcConfig:
         c.ipm_tol_mu, c.ipm_tol_p, c.ipm_tol_d = float(self.ipm_tol_mu), float(self.ipm_tol_p), float(self.ipm_tol_d)
         c.car_width, c.car_length = float(self.car_width), float(self.car_length)
         c.coupling_horizon, c.frame_window = float(self.coupling_horizon), int(self.frame_window)
+        c.ref_speed = float(self.ref_speed)
         return c

@@ -55,7 +55,9 @@ struct mpcb_handle {
             *iters = nullptr, *done = nullptr, *agent_idx = nullptr, *collided = nullptr, *coll_idx = nullptr,
             *n_script = nullptr;
         double *script = nullptr, *obs = nullptr;      // scripted cross traffic [B,8,8] and its last get() rows [B,8,6]
-        bool hasL = false, has_script = false;
+        double* pw = nullptr;                          // per-problem cost weights [B,12]
+        int* vcut = nullptr;                           // mpc_with_speed cutoff_idx [B]
+        bool hasL = false, has_script = false, has_pw = false, has_vcut = false;
         size_t pin_state = 0, pin_diai = 0, pin_status = 0, pin_total = 0;
     } ses;
 };
@@ -128,11 +130,12 @@ namespace {
 constexpr int kHorizons[] = {10, 13, 20, 40, 80};      // <= 31: one warp per problem; longer: one CTA per problem
 constexpr int kLongThreads = 128;
 
-template <int T, int WARPS, int MINB>
+template <int T, int WARPS, int MINB, bool VAR = false>
 int launch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     const size_t smem = sizeof(mpcb::WarpSmem<T>) * WARPS;
     void (*kern)(const StepParams);
-    if constexpr (MINB > 32) kern = mpcb::mpc_step_kernel_r<T, WARPS, MINB>;
+    if constexpr (VAR) kern = mpcb::mpc_step_var_kernel<T, WARPS, MINB>;
+    else if constexpr (MINB > 32) kern = mpcb::mpc_step_kernel_r<T, WARPS, MINB>;
     else kern = mpcb::mpc_step_kernel<T, WARPS, MINB>;
     static thread_local int configured_dev = -1;
     if (configured_dev != h->device) {
@@ -198,6 +201,7 @@ StepParams make_params(const mpcb_handle* h) {
     p.dt = c.dt; p.wheelbase = c.wheelbase; p.max_iter = c.max_iter; p.ipm_max_iter = c.ipm_max_iter;
     p.tol_mu = c.ipm_tol_mu; p.tol_p = c.ipm_tol_p; p.tol_d = c.ipm_tol_d;
     p.goal_dis = c.goal_dis; p.stop_speed = c.stop_speed;
+    p.ref_speed = c.ref_speed;
     return p;
 }
 
@@ -455,6 +459,14 @@ int mpcb_step_host(mpcb_handle* h, int B, const double* state, const int* route,
 namespace {
 
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
+    if (p.pw || p.vcut || p.ref_speed != 0.0) {        // controller variants: their own instantiation
+        switch (h->cfg.T) {
+            case 10: return launch_step<10, 1, 8, true>(h, p, st);
+            case 13: return launch_step<13, 1, 8, true>(h, p, st);
+            case 20: return launch_step<20, 1, 8, true>(h, p, st);
+            default: break;                             // 40, 80: the long-horizon kernel carries them itself
+        }
+    }
     switch (h->cfg.T) {
         case 10: return launch_step<10, 1, 8>(h, p, st);
         case 13:
@@ -494,7 +506,8 @@ int session_alloc(mpcb_handle* h) {
                  o_xdev = put(8 * B), o_goal = put(8 * 2 * B), o_route = put(4 * B), o_nc = put(4 * B),
                  o_tgt = put(4 * B), o_warm = put(4 * B), o_status = put(4 * B), o_iters = put(4 * B),
                  o_done = put(4 * B), o_aidx = put(4 * B), o_coll = put(4 * B), o_cidx = put(4 * B),
-                 o_nscr = put(4 * B), o_script = put(8 * 8 * MPCB_CP_MAX_OBS * B), o_obs = put(8 * 6 * MPCB_CP_MAX_OBS * B);
+                 o_nscr = put(4 * B), o_script = put(8 * 8 * MPCB_CP_MAX_OBS * B), o_obs = put(8 * 6 * MPCB_CP_MAX_OBS * B),
+                 o_pw = put(8 * 12 * B), o_vcut = put(4 * B);
     CUDA_TRY(h, cudaMalloc(&s.slab, o));
     CUDA_TRY(h, cudaMemset(s.slab, 0, o));
     char* d = s.slab;
@@ -505,6 +518,7 @@ int session_alloc(mpcb_handle* h) {
     s.status = (int*)(d + o_status); s.iters = (int*)(d + o_iters); s.done = (int*)(d + o_done);
     s.agent_idx = (int*)(d + o_aidx); s.collided = (int*)(d + o_coll); s.coll_idx = (int*)(d + o_cidx);
     s.n_script = (int*)(d + o_nscr); s.script = (double*)(d + o_script); s.obs = (double*)(d + o_obs);
+    s.pw = (double*)(d + o_pw); s.vcut = (int*)(d + o_vcut);
     o = 0;
     s.pin_state = put(8 * 4 * B); s.pin_diai = put(8 * 2 * B); s.pin_status = put(4 * B);
     s.pin_total = o;
@@ -518,6 +532,7 @@ StepParams session_params(mpcb_handle* h) {
     p.B = s.B; p.state = s.state; p.route = s.route; p.ncourse = s.ncourse; p.L = s.hasL ? s.L : nullptr;
     p.target_ind = s.target; p.warm = s.warm; p.oa = s.oa; p.od = s.od; p.traj = s.traj; p.xref = s.xref;
     p.di_ai = s.di_ai; p.xdev = s.xdev; p.status = s.status; p.iters = s.iters;
+    p.pw = s.has_pw ? s.pw : nullptr; p.vcut = s.has_vcut ? s.vcut : nullptr;
     return p;
 }
 
@@ -543,7 +558,7 @@ int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* 
         if (nc[b] < 1 || nc[b] > h->len_host[r]) { h->err = "mpcb_session_begin: ncourse out of range"; return MPCB_EINVAL; }
         goal[2 * b] = h->goal_host[2 * r]; goal[2 * b + 1] = h->goal_host[2 * r + 1];
     }
-    s.B = B; s.hasL = L_host != nullptr; s.has_script = false;
+    s.B = B; s.hasL = L_host != nullptr; s.has_script = false; s.has_pw = false; s.has_vcut = false;
     cudaStream_t st = h->own_stream;
     CUDA_TRY(h, cudaMemcpyAsync(s.route, route_host, 4 * (size_t)B, cudaMemcpyHostToDevice, st));
     CUDA_TRY(h, cudaMemcpyAsync(s.ncourse, nc.data(), 4 * (size_t)B, cudaMemcpyHostToDevice, st));
@@ -569,6 +584,33 @@ int mpcb_session_set_ncourse_host(mpcb_handle* h, const int* ncourse_host) {
     if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
     CUDA_TRY(h, cudaMemcpyAsync(h->ses.ncourse, ncourse_host, 4 * (size_t)h->ses.B, cudaMemcpyHostToDevice, h->own_stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
+    return MPCB_OK;
+}
+
+int mpcb_session_set_weights_host(mpcb_handle* h, const double* weights_host) {
+    if (!h || h->ses.B <= 0) { if (h) h->err = "mpcb_session_set_weights_host: no session"; return MPCB_EINVAL; }
+    auto& s = h->ses;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
+    if (!weights_host) { s.has_pw = false; return MPCB_OK; }
+    std::vector<double> w(weights_host, weights_host + 12 * (size_t)s.B);
+    for (size_t b = 0; b < (size_t)s.B; ++b)
+        for (int i = 8; i < 12; ++i) w[12 * b + i] *= h->cfg.T;          // Qf = np.diag(config['Qf']) * T (mpc.py:25)
+    CUDA_TRY(h, cudaMemcpyAsync(s.pw, w.data(), 8 * w.size(), cudaMemcpyHostToDevice, h->own_stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
+    s.has_pw = true;
+    return MPCB_OK;
+}
+
+int mpcb_session_set_speed_cutoff_host(mpcb_handle* h, const int* cutoff_idx_host) {
+    if (!h || h->ses.B <= 0) { if (h) h->err = "mpcb_session_set_speed_cutoff_host: no session"; return MPCB_EINVAL; }
+    auto& s = h->ses;
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
+    if (!cutoff_idx_host) { s.has_vcut = false; return MPCB_OK; }
+    CUDA_TRY(h, cudaMemcpyAsync(s.vcut, cutoff_idx_host, 4 * (size_t)s.B, cudaMemcpyHostToDevice, h->own_stream));
+    CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
+    s.has_vcut = true;
     return MPCB_OK;
 }
 

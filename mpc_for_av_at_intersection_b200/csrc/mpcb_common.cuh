@@ -37,6 +37,11 @@ struct StepParams {
     double max_accel, max_decel, max_steer, max_speed, min_speed, r_end, min_ref_speed, dt, wheelbase;
     int max_iter, ipm_max_iter;
     double tol_mu, tol_p, tol_d;
+    // controller variants; all off = main/lib/mpc.py
+    const double* pw;        // [B,12] or null: per-problem w_perp w_para R0 R1 Rd0 Rd1 Qv Qyaw Qf0..3 (Qf scaled by T) --
+                             //   main/lib/mpc_sensitivity.py:150-158 re-reads its JSON on every solve
+    const int* vcut;         // [B] or null: main/lib/mpc_with_speed.py:276-282 cutoff_idx (cv[cutoff_idx:] = 0)
+    double ref_speed;        // cv elsewhere (mpc_with_speed.py:36,280: 25/3.6); xref[2,t] = cv[idx_t] (:104)
 };
 
 namespace mpcb {

@@ -340,7 +340,7 @@ __device__ __forceinline__ void GT_apply(const double (&y)[8], double dt, int la
     gd = y[2] - y[3] - r + shfl_up1(r, lane);
 }
 
-template <int T, int WARPS>
+template <int T, int WARPS, bool VAR>
 __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
     static_assert(T >= 3 && T <= 31, "one warp per problem needs T+1 <= 32");
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -371,6 +371,19 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
     double oa = (warm && act) ? p.oa[(size_t)b * T + lane] : 0.0;     // mpc.py:222-224
     double od = (warm && act) ? p.od[(size_t)b * T + lane] : 0.0;
 
+    // cost weights: the handle's, or this problem's own row (VAR kernels only)
+    double w_perp = p.w_perp, w_para = p.w_para, R0 = p.R0, R1 = p.R1, Rd0 = p.Rd0, Rd1 = p.Rd1, Qv = p.Qv, Qyaw = p.Qyaw,
+           Qf0 = p.Qf0, Qf1 = p.Qf1, Qf2 = p.Qf2, Qf3 = p.Qf3;
+    int vcut = 0x7fffffff;
+    if constexpr (VAR) {
+        if (p.pw) {
+            const double* __restrict__ w = p.pw + 12 * (size_t)b;
+            w_perp = w[0]; w_para = w[1]; R0 = w[2]; R1 = w[3]; Rd0 = w[4]; Rd1 = w[5]; Qv = w[6]; Qyaw = w[7];
+            Qf0 = w[8]; Qf1 = w[9]; Qf2 = w[10]; Qf3 = w[11];
+        }
+        if (p.vcut) vcut = p.vcut[b];
+    }
+    double xr_v = 0.0;                                 // xref[2, lane]: speed reference (mpc_with_speed.py:104), else 0
     int status = MPCB_ST_OPTIMAL, iters = 0;
     bool solved = false, have_ov = false;
     double sx = 0.0, sy = 0.0, sv = 0.0, sph = 0.0;    // solution states at index lane (0..T)
@@ -405,6 +418,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
         if (lane > T) idx = nc - 1;
         idx = max(idx, 0);
         xr_x = cx[idx]; xr_y = cy[idx]; xr_yaw = cyaw[idx];
+        if constexpr (VAR) xr_v = idx < vcut ? p.ref_speed : 0.0;
         const bool reach = (idx == nc - 1);
 
         // ---- A3: rollout of the previous (unshifted) solution: operating point (vbar, phibar) -------
@@ -437,6 +451,8 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
 
         // ---- A5: stage weights for state lane+1, input weights for stage lane -------------------------
         const double rx = shfl_dn1(xr_x, lane), ry = shfl_dn1(xr_y, lane), rpsi = shfl_dn1(xr_yaw, lane);
+        double rv = 0.0;
+        if constexpr (VAR) rv = shfl_dn1(xr_v, lane);
         const bool reach_n = __shfl_down_sync(MPCB_FULL, (int)reach, 1) != 0;
         double m11 = 0.0, m12 = 0.0, m22 = 0.0, wv = 0.0, wp = 0.0;
         if (act) {
@@ -444,14 +460,14 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                 double s1, c1, s2, c2;
                 sincos(rpsi + 0.5 * 3.141592653589793, &s1, &c1);     // mpc.py:160
                 sincos(rpsi, &s2, &c2);                                // mpc.py:164
-                m11 = p.w_perp * (c1 * c1) + p.w_para * (c2 * c2);
-                m12 = p.w_perp * (c1 * s1) + p.w_para * (c2 * s2);
-                m22 = p.w_perp * (s1 * s1) + p.w_para * (s2 * s2);
-                wv = p.Qv; wp = p.Qyaw;
-            } else { m11 = p.Qf0; m22 = p.Qf1; wv = p.Qf2; wp = p.Qf3; }
+                m11 = w_perp * (c1 * c1) + w_para * (c2 * c2);
+                m12 = w_perp * (c1 * s1) + w_para * (c2 * s2);
+                m22 = w_perp * (s1 * s1) + w_para * (s2 * s2);
+                wv = Qv; wp = Qyaw;
+            } else { m11 = Qf0; m22 = Qf1; wv = Qf2; wp = Qf3; }
         }
-        const double ra_w = act ? (reach ? p.r_end : p.R0) : 0.0;     // mpc.py:177-180
-        const double rd_w = act ? (reach ? p.r_end : p.R1) : 0.0;
+        const double ra_w = act ? (reach ? p.r_end : R0) : 0.0;     // mpc.py:177-180
+        const double rd_w = act ? (reach ? p.r_end : R1) : 0.0;
 
         // ---- condensed Hessian from suffix moments ----------------------------------------------------
         const double Zx = scan_up(c_, lane), Zy = scan_up(s_, lane);
@@ -488,8 +504,8 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                 const double Blo = hB + zxj * gCx + zyj * gCy;
                 const double Bup = sm.bc[5][j] + Wx * sm.bc[6][j] + Wy * sm.bc[7][j];
                 const double Bij = kB * ((j <= lane) ? Blo : Bup);
-                if (j == lane) { Aij += 2.0 * ra_w + 2.0 * p.Rd0 * nb; Cij += 2.0 * rd_w + 2.0 * p.Rd1 * nb; }
-                if (j == lane - 1) { Aij -= 2.0 * p.Rd0; Cij -= 2.0 * p.Rd1; }
+                if (j == lane) { Aij += 2.0 * ra_w + 2.0 * Rd0 * nb; Cij += 2.0 * rd_w + 2.0 * Rd1 * nb; }
+                if (j == lane - 1) { Aij -= 2.0 * Rd0; Cij -= 2.0 * Rd1; }
                 if (act) {
                     sm.HB[WarpSmem<T>::colB(j) + lane] = Bij;
                     if (j <= lane) {                             // symmetric blocks: both triangles are stored
@@ -529,7 +545,8 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
             predict(a, d, xs, ys, vs, phs);
             const double ex = xs - rx, ey = ys - ry;
             const double lx = 2.0 * (m11 * ex + m12 * ey), ly = 2.0 * (m12 * ex + m22 * ey);
-            const double lv = 2.0 * wv * vs, lp = 2.0 * wp * (phs - rpsi);      // xref[2,:] = 0 (mpc.py:102-105)
+            // xref[2,:] = 0 in main/lib/mpc.py:102-105 (rv == 0); cv[idx] in mpc_with_speed.py:104
+            const double lv = 2.0 * wv * (VAR ? vs - rv : vs), lp = 2.0 * wp * (phs - rpsi);
             const double px = scan_dn(lx, lane), py = scan_dn(ly, lane);
             const double pxn = shfl_dn1(px, lane), pyn = shfl_dn1(py, lane);
             const double pv = scan_dn(lv + cn * pxn + snn * pyn, lane);
@@ -538,8 +555,8 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
             const double dp = shfl_up1(d, lane), dn = shfl_dn1(d, lane);
             const double fa = (lane > 0 ? a - ap : 0.0) - (lane < T - 1 ? an - a : 0.0);
             const double fd = (lane > 0 ? d - dp : 0.0) - (lane < T - 1 ? dn - d : 0.0);
-            ga = act ? dt * pv + 2.0 * ra_w * a + 2.0 * p.Rd0 * fa : 0.0;
-            gd = act ? bb * pph + 2.0 * rd_w * d + 2.0 * p.Rd1 * fd : 0.0;
+            ga = act ? dt * pv + 2.0 * ra_w * a + 2.0 * Rd0 * fa : 0.0;
+            gd = act ? bb * pph + 2.0 * rd_w * d + 2.0 * Rd1 * fd : 0.0;
         };
 
         // ---- A6: interior point on  min J(u)  s.t.  G u <= h ----------------------------------------------
@@ -876,7 +893,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
     if (p.xref && lane <= T) {
         p.xref[tb + lane] = xr_x;
         p.xref[tb + (T + 1) + lane] = xr_y;
-        p.xref[tb + 2 * (T + 1) + lane] = 0.0;
+        p.xref[tb + 2 * (T + 1) + lane] = xr_v;
         p.xref[tb + 3 * (T + 1) + lane] = xr_yaw;
     }
     const double qnan = __longlong_as_double(0x7ff8000000000000LL);
@@ -941,9 +958,14 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
 // Register budget: REGS <= 32 is a minimum-resident-CTA hint (__launch_bounds__), REGS > 32 an explicit cap per
 // thread (__maxnreg__; ptxas quantises the launch-bounds form much more coarsely than the hardware allocates).
 template <int T, int WARPS, int MINB>
-__global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepParams p) { mpc_step_body<T, WARPS>(p); }
+__global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepParams p) { mpc_step_body<T, WARPS, false>(p); }
 
 template <int T, int WARPS, int REGS>
-__global__ void __maxnreg__(REGS) mpc_step_kernel_r(const StepParams p) { mpc_step_body<T, WARPS>(p); }
+__global__ void __maxnreg__(REGS) mpc_step_kernel_r(const StepParams p) { mpc_step_body<T, WARPS, false>(p); }
+
+// The controller variants of SURVEY 8f N3 (speed reference of main/lib/mpc_with_speed.py, per-problem cost weights of
+// main/lib/mpc_sensitivity.py) as a second instantiation, so that the default kernel's code is untouched.
+template <int T, int WARPS, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_var_kernel(const StepParams p) { mpc_step_body<T, WARPS, true>(p); }
 
 }  // namespace mpcb

@@ -211,6 +211,20 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
     double oa = (warm && act) ? p.oa[(size_t)b * T + tid] : 0.0;     // mpc.py:222-224
     double od = (warm && act) ? p.od[(size_t)b * T + tid] : 0.0;
 
+    constexpr bool VAR = true;      // the long-horizon kernel always carries the variants (it is not register-bound)
+    // cost weights: the handle's, or this problem's own row (VAR kernels only)
+    double w_perp = p.w_perp, w_para = p.w_para, R0 = p.R0, R1 = p.R1, Rd0 = p.Rd0, Rd1 = p.Rd1, Qv = p.Qv, Qyaw = p.Qyaw,
+           Qf0 = p.Qf0, Qf1 = p.Qf1, Qf2 = p.Qf2, Qf3 = p.Qf3;
+    int vcut = 0x7fffffff;
+    if constexpr (VAR) {
+        if (p.pw) {
+            const double* __restrict__ w = p.pw + 12 * (size_t)b;
+            w_perp = w[0]; w_para = w[1]; R0 = w[2]; R1 = w[3]; Rd0 = w[4]; Rd1 = w[5]; Qv = w[6]; Qyaw = w[7];
+            Qf0 = w[8]; Qf1 = w[9]; Qf2 = w[10]; Qf3 = w[11];
+        }
+        if (p.vcut) vcut = p.vcut[b];
+    }
+    double xr_v = 0.0;                                 // xref[2, lane]: speed reference (mpc_with_speed.py:104), else 0
     int status = MPCB_ST_OPTIMAL, iters = 0;
     bool solved = false, have_ov = false;
     double sx = 0.0, sy = 0.0, sv = 0.0, sph = 0.0;    // solution states at index tid (0..T)
@@ -246,6 +260,7 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
         if (tid > T) ix = nc - 1;
         ix = max(ix, 0);
         xr_x = cx[ix]; xr_y = cy[ix]; xr_yaw = cyaw[ix];
+        xr_v = ix < vcut ? p.ref_speed : 0.0;
         const bool reach = (ix == nc - 1);
 
         // ---- A3: rollout of the previous (unshifted) solution (main/lib/mpc.py:112-126) ---------------------
@@ -279,7 +294,7 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
         const double cn = bo.dn1(c_), snn = bo.dn1(s_), ppn = bo.dn1(pp), qqn = bo.dn1(qq);
 
         // ---- A5: stage weights for state tid+1, input weights for stage tid (main/lib/mpc.py:151-184) ------
-        const double rx = bo.dn1(xr_x), ry = bo.dn1(xr_y), rpsi = bo.dn1(xr_yaw);
+        const double rx = bo.dn1(xr_x), ry = bo.dn1(xr_y), rpsi = bo.dn1(xr_yaw), rv = bo.dn1(xr_v);
         const bool reach_n = bo.dn1i((int)reach) != 0;
         double m11 = 0.0, m12 = 0.0, m22 = 0.0, wv = 0.0, wp = 0.0;
         if (act) {
@@ -287,14 +302,14 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
                 double s1, c1, s2, c2;
                 sincos(rpsi + 0.5 * 3.141592653589793, &s1, &c1);
                 sincos(rpsi, &s2, &c2);
-                m11 = p.w_perp * (c1 * c1) + p.w_para * (c2 * c2);
-                m12 = p.w_perp * (c1 * s1) + p.w_para * (c2 * s2);
-                m22 = p.w_perp * (s1 * s1) + p.w_para * (s2 * s2);
-                wv = p.Qv; wp = p.Qyaw;
-            } else { m11 = p.Qf0; m22 = p.Qf1; wv = p.Qf2; wp = p.Qf3; }
+                m11 = w_perp * (c1 * c1) + w_para * (c2 * c2);
+                m12 = w_perp * (c1 * s1) + w_para * (c2 * s2);
+                m22 = w_perp * (s1 * s1) + w_para * (s2 * s2);
+                wv = Qv; wp = Qyaw;
+            } else { m11 = Qf0; m22 = Qf1; wv = Qf2; wp = Qf3; }
         }
-        const double ra_w = act ? (reach ? p.r_end : p.R0) : 0.0;
-        const double rd_w = act ? (reach ? p.r_end : p.R1) : 0.0;
+        const double ra_w = act ? (reach ? p.r_end : R0) : 0.0;
+        const double rd_w = act ? (reach ? p.r_end : R1) : 0.0;
 
         // ---- per-stage moment tables of the condensed Hessian ------------------------------------------------
         const double Zx = bo.scan_up(c_), Zy = bo.scan_up(s_);
@@ -321,7 +336,7 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
                 sm.t(LT_BB)[tid] = bb; sm.t(LT_HH)[tid] = hh;
                 sm.t(LT_GAX)[tid] = gAx; sm.t(LT_GAY)[tid] = gAy; sm.t(LT_GCX)[tid] = gCx; sm.t(LT_GCY)[tid] = gCy;
                 sm.t(LT_HA)[tid] = hA; sm.t(LT_HC)[tid] = hC; sm.t(LT_HB)[tid] = hB;
-                sm.t(LT_DGA)[tid] = 2.0 * ra_w + 2.0 * p.Rd0 * nb; sm.t(LT_DGC)[tid] = 2.0 * rd_w + 2.0 * p.Rd1 * nb;
+                sm.t(LT_DGA)[tid] = 2.0 * ra_w + 2.0 * Rd0 * nb; sm.t(LT_DGC)[tid] = 2.0 * rd_w + 2.0 * Rd1 * nb;
             }
             __syncthreads();
         }
@@ -343,7 +358,7 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
             predict(a, d, xs, ys, vs, phs);
             const double ex = xs - rx, ey = ys - ry;
             const double lx = 2.0 * (m11 * ex + m12 * ey), ly = 2.0 * (m12 * ex + m22 * ey);
-            const double lv = 2.0 * wv * vs, lp = 2.0 * wp * (phs - rpsi);      // xref[2,:] = 0 (mpc.py:102-105)
+            const double lv = 2.0 * wv * (vs - rv), lp = 2.0 * wp * (phs - rpsi);      // rv = 0: xref[2,:] = 0 (mpc.py:102-105)
             const double px = bo.scan_dn(act ? lx : 0.0), py = bo.scan_dn(act ? ly : 0.0);
             const double pxn = bo.dn1(px), pyn = bo.dn1(py);
             const double pv = bo.scan_dn(act ? lv + cn * pxn + snn * pyn : 0.0);
@@ -352,8 +367,8 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
             const double dp = bo.up1(d), dn = bo.dn1(d);
             const double fa = (tid > 0 ? a - ap : 0.0) - (tid < T - 1 ? an - a : 0.0);
             const double fd = (tid > 0 ? d - dp : 0.0) - (tid < T - 1 ? dn - d : 0.0);
-            ga = act ? dt * pv + 2.0 * ra_w * a + 2.0 * p.Rd0 * fa : 0.0;
-            gd = act ? bb * pph + 2.0 * rd_w * d + 2.0 * p.Rd1 * fd : 0.0;
+            ga = act ? dt * pv + 2.0 * ra_w * a + 2.0 * Rd0 * fa : 0.0;
+            gd = act ? bb * pph + 2.0 * rd_w * d + 2.0 * Rd1 * fd : 0.0;
         };
         // structured constraint operator, slots as in mpcb_step.cuh (main/lib/mpc.py:184,187-191)
         auto G_apply = [&](double a, double d, double (&g)[8]) {
@@ -451,7 +466,7 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
                         for (int j = lane; j <= i; j += 32) {
                             double v = kA * (hA + sm.t(LT_ZX)[j] * gAx + sm.t(LT_ZY)[j] * gAy) + wvs;
                             if (j == i) v += sm.t(LT_DGA)[i] + sm.t(LT_DA)[i];
-                            if (j == i - 1) v -= 2.0 * p.Rd0;
+                            if (j == i - 1) v -= 2.0 * Rd0;
                             row[j] = v;
                         }
                     } else {                                       // steer row r = i - T
@@ -467,7 +482,7 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
                         for (int j = lane; j <= r; j += 32) {      // steer block: steer column j <= r
                             double v = kC * sm.t(LT_BB)[j] * (hC + sm.t(LT_WX)[j] * gCx + sm.t(LT_WY)[j] * gCy);
                             if (j == r) v += sm.t(LT_DGC)[r] + sm.t(LT_DC)[r];
-                            if (j == r - 1) v -= 2.0 * p.Rd1 + sm.t(LT_WRP)[r];
+                            if (j == r - 1) v -= 2.0 * Rd1 + sm.t(LT_WRP)[r];
                             row[T + j] = v;
                         }
                     }
@@ -592,7 +607,7 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
     if (p.xref && tid <= T) {
         p.xref[tb + tid] = xr_x;
         p.xref[tb + (T + 1) + tid] = xr_y;
-        p.xref[tb + 2 * (T + 1) + tid] = 0.0;
+        p.xref[tb + 2 * (T + 1) + tid] = xr_v;
         p.xref[tb + 3 * (T + 1) + tid] = xr_yaw;
     }
     const double qnan = __longlong_as_double(0x7ff8000000000000LL);

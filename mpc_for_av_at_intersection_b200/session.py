@@ -116,6 +116,27 @@ class MpcSession:
             self._h, int(nsteps), int(vehicles_per_scenario), C.c_void_p(history_ptr) if history_ptr else None,
             0 if goal_test else 1, C.c_void_p(cuda_stream)), self._h, "mpcb_session_multi_agent_dev")
 
+    # ---- controller variants --------------------------------------------------------------------
+    def set_weights(self, weights):
+        """Per-problem cost weights [B,12] (MpcConfig.weight_row order, file units) -- the batched form of
+        main/lib/mpc_sensitivity.py re-reading its JSON on every solve; None = the session's config for everyone."""
+        if weights is None:
+            _lib.check(self._lib.mpcb_session_set_weights_host(self._h, None), self._h, "mpcb_session_set_weights_host")
+            return
+        w = np.ascontiguousarray(weights, dtype=np.float64)
+        assert w.shape == (self.B, 12), w.shape
+        _lib.check(self._lib.mpcb_session_set_weights_host(self._h, _p(w)), self._h, "mpcb_session_set_weights_host")
+
+    def set_speed_cutoff(self, cutoff_idx):
+        """mpc_with_speed.MPC.set_trajectory_fromarray(traj, cutoff_idx) for the batch (main/lib/mpc_with_speed.py:
+        276-282): the speed reference drops to 0 from cutoff_idx[b] on; 999 (the reference's sentinel) or None = no cut."""
+        if cutoff_idx is None:
+            _lib.check(self._lib.mpcb_session_set_speed_cutoff_host(self._h, None), self._h, "mpcb_session_set_speed_cutoff_host")
+            return
+        c = np.ascontiguousarray(cutoff_idx, dtype=np.int32)
+        assert c.shape == (self.B,)
+        _lib.check(self._lib.mpcb_session_set_speed_cutoff_host(self._h, _p(c)), self._h, "mpcb_session_set_speed_cutoff_host")
+
     def set_scripted_obstacles(self, scripts):
         """scripts: per ego a list of (direction, turning, speed, offset) tuples -- the constructor arguments of the
         reference's `MovingObstacleTIntersection` (main/lib/moving_obstacles.py:165-196; offset None or <= 0 = starts

@@ -126,3 +126,56 @@ def test_max_iter_3_matches_oracle():
         worst = max(worst, abs(di - di_ai[b, 0]), abs(ai - di_ai[b, 1]), np.abs(om.ox - out["traj"][b, 0]).max())
     print(f"MAX_ITER=3: max deviation {worst:.2e}")
     assert worst < 1e-6
+
+
+# ---- controller variants through the resident session ---------------------------------------------
+def _run_session(cfg, g, sel, weights=None, vcut=None):
+    """One MPC.step per golden row through MpcSession (store the recorded object state, step, fetch)."""
+    from mpc_for_av_at_intersection_b200 import CourseSet, MpcSession
+    ses = MpcSession(cfg, CourseSet(load_routes(False)), len(sel))
+    ses.begin(g["route"][sel].astype(np.int32), ncourse=g["ncourse"][sel].astype(np.int32),
+              target_ind=g["target_in"][sel].astype(np.int32), L=g["L"][sel] if "L" in g.files else None)
+    ses.store("warm", g["has_warm"][sel].astype(np.int32))
+    ses.store("oa", np.nan_to_num(g["oa_in"][sel]))
+    ses.store("odelta", np.nan_to_num(g["od_in"][sel]))
+    ses.store("di_ai", np.stack([g["di_in"][sel], g["ai_in"][sel]], axis=1))
+    if weights is not None:
+        ses.set_weights(weights)
+    if vcut is not None:
+        ses.set_speed_cutoff(vcut)
+    before = ses.launches
+    ses.step(np.ascontiguousarray(g["state"][sel]))
+    assert ses.launches == before + 1
+    out = dict(target=ses.fetch("target_ind"), xref=ses.fetch("xref"), status=ses.status.copy(), warm=ses.fetch("warm"),
+               oa=ses.fetch("oa"), od=ses.fetch("odelta"), di_ai=ses.fetch("di_ai"), traj=ses.fetch("traj"),
+               xdev=ses.fetch("xref_deviation"), iters=ses.fetch("iters"))
+    ses.close()
+    return out
+
+
+def test_mpc_with_speed_variant_matches_reference():
+    """main/lib/mpc_with_speed.py (speed reference cv with the per-step cutoff index, its hard-coded weights) through
+    the variant kernel: every step of the reference's mpc_intersection_new_ref.py loop + 150 randomised steps."""
+    from mpc_for_av_at_intersection_b200 import MpcConfig
+    g = golden("variant_with_speed.npz")
+    sel = np.arange(len(g["state"]))
+    out = _run_session(MpcConfig.with_speed(), g, sel, vcut=g["cutoff_idx"][sel].astype(np.int32))
+    assert (out["xref"][:, 2] == 0).any() and (out["xref"][:, 2] > 6.9).any()
+    _compare(g, sel, out, 13)
+
+
+def test_mpc_sensitivity_variant_is_one_batch():
+    """main/lib/mpc_sensitivity.py re-reads its weights on every solve so that a script can sweep them one run after
+    the other; here all 30 (parameter, value) settings x 25 steps are ONE launch with per-problem weight rows."""
+    from mpc_for_av_at_intersection_b200 import MpcConfig
+    g = golden("variant_sensitivity.npz")
+    sel = np.arange(len(g["state"]))
+    out = _run_session(MpcConfig.from_json(T=13), g, sel, weights=g["weights"][sel])
+    _compare(g, sel, out, 13)
+    # T = 40 takes the long-horizon kernel, which carries the variants too: per-problem rows equal to the handle's
+    # config must reproduce the plain golden steps
+    g40 = golden("random_T40.npz")
+    cfg40 = MpcConfig.from_json(T=40)
+    sel = np.arange(len(g40["state"]))
+    out = _run_session(cfg40, g40, sel, weights=np.tile(cfg40.weight_row(), (len(sel), 1)))
+    _compare(g40, sel, out, 40)

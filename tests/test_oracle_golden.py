@@ -85,3 +85,53 @@ def test_condensed_model_agrees_with_oracle(routes_smooth):
             assert np.abs((gj - g0) - H[:, j]).max() < 1e-8 * max(1.0, np.abs(H[:, j]).max())
         checked += 1
     assert checked >= 5
+
+
+# ---- controller variants: oracle vs the reference's mpc_with_speed / mpc_sensitivity -------------
+WITH_SPEED = {"T": 13, "w_perp": 10.0, "w_para": 1.0, "R": [0.01, 0.01], "Rd": [0.01, 1.0], "Q_v_yaw": [20.0, 0.5],
+              "Qf": [1.0, 1.0, 0.0, 0.5], "GOAL_DIS": 1.5, "STOP_SPEED": 0.5 / 3.6, "MAX_DSTEER": 30.0, "MAX_ACCEL": 2.0,
+              "MAX_DECEL": -5}          # main/lib/mpc_with_speed.py:16-36,161,165
+
+
+def _replay_variant(g, k, routes_smooth, cfgd, ref_speed=None):
+    r = int(g["route"][k])
+    full = routes_smooth[r]
+    om = mo.OracleMPC(full[:, 0].copy(), full[:, 1].copy(), full[:, 2].copy(),
+                      float(np.linalg.norm(full[0, :2] - full[1, :2])), 2.86, 0.2, mo.Cfg.from_dict(cfgd))
+    om.ref_speed = ref_speed
+    om.set_trajectory_fromarray(full, int(g["cutoff_idx"][k]) if "cutoff_idx" in g.files else 999)
+    om.target_ind = int(g["target_in"][k])
+    if g["has_warm"][k]:
+        om.oa, om.odelta = g["oa_in"][k].copy(), g["od_in"][k].copy()
+    om.di, om.ai = float(g["di_in"][k]), float(g["ai_in"][k])
+    om.step(g["state"][k])
+    return om
+
+
+def _check_variant(om, g, k):
+    assert om.target_ind == int(g["target_out"][k])
+    assert np.array_equal(om.xref, g["xref"][k])
+    assert (om.odelta is not None) == bool(g["solved"][k])
+    if g["solved"][k]:
+        assert np.abs(om.oa - g["oa"][k]).max() < 1e-6 and np.abs(om.odelta - g["od"][k]).max() < 1e-6
+        return max(abs(om.di - g["di"][k]), abs(om.ai - g["ai"][k]))
+    return 0.0
+
+
+def test_oracle_matches_reference_mpc_with_speed(routes_smooth):
+    g = golden("variant_with_speed.npz")
+    assert (g["cutoff_idx"] != 999).sum() > 50 and (g["xref"][:, 2] == 0).any() and (g["xref"][:, 2] > 6.9).any()
+    worst = max(_check_variant(_replay_variant(g, k, routes_smooth, WITH_SPEED, 25 / 3.6), g, k)
+                for k in range(0, len(g["state"]), 3))
+    assert worst < 1e-7, worst
+
+
+def test_oracle_matches_reference_mpc_sensitivity(routes_smooth):
+    g = golden("variant_sensitivity.npz")
+    assert int(g["n_cases"]) == 30
+    worst = 0.0
+    for k in range(0, len(g["state"]), 9):
+        w = g["weights"][k]
+        cfgd = {"T": 13, "w_perp": w[0], "w_para": w[1], "R": w[2:4], "Rd": w[4:6], "Q_v_yaw": w[6:8], "Qf": w[8:12]}
+        worst = max(worst, _check_variant(_replay_variant(g, k, routes_smooth, cfgd), g, k))
+    assert worst < 1e-7, worst
