@@ -1,6 +1,8 @@
 """Host logic of the reference-compatible faces (no GPU): module constants follow main/lib/mpc.py:17-36, the
 scalar Simulation/History reproduce the reference's plant (checked against the golden histories), CarDimensions
 numbers follow main/lib/car_dimensions.py."""
+import os
+
 import numpy as np
 
 from conftest import golden
@@ -111,3 +113,39 @@ def test_flop_model_matches_survey_table():
     for T, want in ((10, 0.11e6), (13, 0.20e6), (20, 0.60e6), (40, 3.95e6), (80, 28.7e6)):
         got = bench.algorithmic_flops(T, 660, 15)
         assert abs(got - want) / want < 0.06, (T, got, want)
+
+
+def test_result_formats_from_device_rows(tmp_path):
+    """a [steps, B, 8] device block -> per-vehicle History identical to the one HistorySimulation builds
+    when fed the same steps; CSV / NPZ exports and the figure series of visualize_final / plot_trajectories."""
+    from conftest import golden
+    from mpc_for_av_at_intersection_b200 import results
+    from mpc_for_av_at_intersection_b200.compat.simulation import History
+    g = golden("closed_loop_T13.npz")
+    off = g["history_off"]
+    loops = [0, 12]
+    n = [int(off[i + 1] - off[i]) - 1 for i in loops]
+    K = max(n) + 2
+    rows = np.full((K, 2, 8), np.nan)
+    for j, i in enumerate(loops):
+        ref = g["history"][off[i]:off[i + 1]]                 # x y yaw v delta a dev, row 0 = initial state
+        rows[:n[j], j, :7] = ref[1:]
+        rows[:n[j], j, 7] = 0
+    state0 = np.stack([g["history"][off[i], :4] for i in loops])
+    hs = results.histories_from_device(rows, state0, 0.2)
+    for j, i in enumerate(loops):
+        ref = g["history"][off[i]:off[i + 1]]
+        tab = results.history_table(hs[j])
+        assert tab.shape == (n[j] + 1, 8)
+        assert np.array_equal(tab[:, [0, 1, 2, 3, 5, 6, 7]], ref)
+        assert np.allclose(tab[:, 4], 0.2 * np.arange(1, n[j] + 2))      # History.store adds dt before storing (simulation.py:77-78)
+    sel = np.flatnonzero(g["loop"] == 12)
+    files = results.export_run(str(tmp_path / "run"), hs[1], g["obs"][sel], 0.2)
+    assert len(files) >= 7 and all(os.path.getsize(f) > 0 for f in files)
+    sp = np.loadtxt(tmp_path / "run" / "final_speed.csv", delimiter=",", skiprows=1)
+    assert np.allclose(sp[:, 1], np.array(hs[1].v) * 3.6)
+    tr = np.loadtxt(tmp_path / "run" / "trajectory_obstacle_1.csv", delimiter=",", skiprows=1)
+    assert tr.shape == (len(sel), 3) and tr[0, 1] == 30.0
+    results.save_sweep_npz(str(tmp_path / "sweep.npz"), rows, state0, [0, 9])
+    z = np.load(tmp_path / "sweep.npz")
+    assert list(z["steps"]) == n and z["history"].shape == rows.shape and z["mean_xref_deviation"].shape == (2,)
