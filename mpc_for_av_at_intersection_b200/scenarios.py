@@ -87,3 +87,23 @@ def make_multi_agent_workload(courses, n_scenarios, vehicles=8, seed=1236, first
         state[sl, 0], state[sl, 1], state[sl, 2] = courses.packed[r, 0, i0], courses.packed[r, 1, i0], courses.packed[r, 2, i0]
         state[sl, 3] = rng.uniform(0.0, v_max, vehicles)
     return dict(route=route, state=state, target_ind=np.maximum(index0 - 3, 0).astype(np.int32), index0=index0)
+
+
+def make_scripted_workload(courses, n, seed=1237, first=0, max_cars=3, v_max=4.0):
+    """ego vehicles starting at the head of a random route (speed U[0, v_max]) with 0..max_cars
+    scripted crossing cars each -- the constructor arguments of the reference's MovingObstacleTIntersection
+    (main/lib/moving_obstacles.py:165-196; the reference scenario uses two, main/scenarios/mpc_intersection.py:41-44):
+    direction +-1, turning or straight, speed U[3, 9] m/s, start offset 0 or U[0.2, 3] s.
+    Returns dict(route, state, target_ind, scripts [n, 8, 4] with NaN rows past each ego's count)."""
+    route = np.empty(n, np.int32)
+    state = np.empty((n, 4))
+    scripts = np.full((n, 8, 4), np.nan)
+    for k in range(n):
+        rng = np.random.Generator(np.random.Philox(key=[np.uint64(seed), np.uint64(first + k)]))
+        r = int(rng.integers(0, courses.R))
+        route[k] = r
+        state[k] = (courses.packed[r, 0, 0], courses.packed[r, 1, 0], courses.packed[r, 2, 0], rng.uniform(0.0, v_max))
+        for o in range(int(rng.integers(0, max_cars + 1))):
+            scripts[k, o] = (float(rng.choice([-1, 1])), float(rng.integers(0, 2)), rng.uniform(3.0, 9.0),
+                             float(rng.choice([0.0, rng.uniform(0.2, 3.0)])))
+    return dict(route=route, state=state, target_ind=np.zeros(n, np.int32), scripts=scripts)
