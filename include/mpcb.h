@@ -262,6 +262,36 @@ int mpcb_session_scripted_loop_dev(mpcb_handle* h, int nsteps, double* history_d
 #define MPCB_F_OBS 19       /* double [B,MPCB_MAX_OBSTACLES,6] last get() rows (when no obs_history_dev was given) */
 #define MPCB_F_NOBS 20      /* int    [B] scripted obstacles per ego */
 
+/* ---- motion-primitive A* planner ------------------------------------------------------
+ * replaces: `MotionPrimitiveSearch(scenario, car_dimensions, mps, margin).run()` (main/lib/motion_primitive_search_modified.py:
+ * 18-58) = the A* loop of main/lib/a_star.py:31-78 over the neighbour function :101-149 (collision check of every
+ * primitive's circle-centre points against the obstacles' half-planes, main/lib/obstacles.py:157-176), the goal test
+ * and heuristic :64-86 and the trajectory assembly :151-165 -- for B searches at once, one warp per search.
+ * All pointers are HOST memory; synchronous; no handle (the planner runs once per vehicle, before the MPC loop).
+ *   start, goal      [B,3]  (x, y, theta): Scenario.start, Scenario.goal_point (main/lib/scenario.py:7-13)
+ *   goal_box         [B,4]  x1, y1, x2, y2 of Scenario.goal_area (a BoxObstacle, obstacles.py:46-58)
+ *   allowed          [B]    Scenario.allowed_goal_theta_difference
+ *   obs_set          [B]    which obstacle set each search uses (0..S-1)
+ *   halfplanes       [S,32,8,3], n_halfplanes [S,32], n_obstacles [S]: Obstacle.to_convex(margin) rows (a, b, c) --
+ *                    a point is inside an obstacle where a x + b y + c <= 0 for every row (obstacles.py:96-105,135-151)
+ *   mp_points        [P,NP,3] primitive points (x, y, theta) in the primitive's start frame, mp_n_points [P] valid points,
+ *                    mp_length [P] MotionPrimitive.total_length; P <= 16, in the order the reference iterates `mps`
+ *   mp_cc_points     [P,NCC,2] circle-centre collision points of every primitive (:35-52), NCC <= 16
+ *   max_open, max_closed, max_path: capacities of the open list, the closed set and the path (nodes) per search
+ * Outputs: status [B] MPCB_PLAN_*, cost [B] (NaN unless OK), n_path [B] nodes on the path, mp_seq [B,max_path]
+ * primitive index per edge (-1 padded), nodes [B,max_path,3], n_expanded [B] (nodes taken off the queue and kept,
+ * = len(debug_data)), n_pushed [B]; traj [B,(max_path-1)*(NP-1),3] + n_traj [B] or NULL. */
+#define MPCB_PLAN_OK 0
+#define MPCB_PLAN_NO_SOLUTION 1   /* Exception("No solution found.") (main/lib/a_star.py:78) */
+#define MPCB_PLAN_OVERFLOW 2      /* a capacity was too small: enlarge max_open / max_closed / max_path */
+int mpcb_plan_routes_host(int device, int B, const double* start, const double* goal, const double* goal_box,
+                          const double* allowed, const int* obs_set, int S, const double* halfplanes, const int* n_halfplanes,
+                          const int* n_obstacles, int P, int NP, const double* mp_points, const int* mp_n_points,
+                          const double* mp_length, int NCC, const double* mp_cc_points, int max_open, int max_closed,
+                          int max_path, int* status, double* cost, int* n_path, int* mp_seq, double* nodes, int* n_expanded,
+                          int* n_pushed, double* traj, int* n_traj);
+const char* mpcb_plan_last_error(void);
+
 /* kernels launched by this handle so far (bench.py's gpu_launches) */
 long long mpcb_launch_count(const mpcb_handle* h);
 

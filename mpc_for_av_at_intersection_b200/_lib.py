@@ -42,6 +42,7 @@ EXPORTS = [
     "mpcb_coupling", "mpcb_coupling_host", "mpcb_session_multi_agent_dev",
     "mpcb_session_set_scripted_host", "mpcb_session_scripted_loop_dev",
     "mpcb_session_set_weights_host", "mpcb_session_set_speed_cutoff_host",
+    "mpcb_plan_routes_host", "mpcb_plan_last_error",
 ]
 
 F_STATE, F_OA, F_OD, F_TRAJ, F_XREF, F_DI_AI, F_XDEV, F_TARGET, F_WARM, F_STATUS, F_ITERS, F_DONE, F_NCOURSE, \
@@ -134,6 +135,11 @@ def lib():
     L.mpcb_session_set_weights_host.restype = C.c_int
     L.mpcb_session_set_speed_cutoff_host.argtypes = [vp, vp]
     L.mpcb_session_set_speed_cutoff_host.restype = C.c_int
+    L.mpcb_plan_routes_host.argtypes = [C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, vp, vp, vp,
+                                        C.c_int, vp, C.c_int, C.c_int, C.c_int] + [vp] * 9
+    L.mpcb_plan_routes_host.restype = C.c_int
+    L.mpcb_plan_last_error.argtypes = []
+    L.mpcb_plan_last_error.restype = C.c_char_p
     L.mpcb_launch_count.argtypes = [vp]
     L.mpcb_launch_count.restype = C.c_longlong
     L.mpcb_measure_fp64_peak.argtypes = [C.c_int, dp]
