@@ -12,6 +12,7 @@ timeout 300 python __graft_entry__.py smoke > $OUT/smoke_$TAG.log 2>&1; echo "sm
 timeout 600 python bench.py > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.err; echo "bench rc=$?"; cat $OUT/bench_$TAG.json; tail -5 $OUT/bench_$TAG.err
 timeout 300 python bench.py --impl reference --steps 10 > $OUT/bench_ref_$TAG.json 2>> $OUT/bench_$TAG.err; cat $OUT/bench_ref_$TAG.json
 timeout 300 python bench.py --batch 65536 --steps 10 --no-cpu-baseline > $OUT/bench_b65536_$TAG.json 2>> $OUT/bench_$TAG.err; cat $OUT/bench_b65536_$TAG.json
+timeout 600 python scripts/bench_planner.py > $OUT/planner_$TAG.json 2>> $OUT/bench_$TAG.err; cat $OUT/planner_$TAG.json
 CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline"
 timeout 300 $CMD > $OUT/plain_$TAG.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_launches_$TAG.log 2>&1
