@@ -576,7 +576,9 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
                     tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
                 }
                 tmax = bo.max(tmax);
-                const double al = (tmax > 0.99) ? 0.99 / tmax : 1.0;
+                // adaptive fraction to the boundary, see mpcb_step.cuh
+                const double eta = 1.0 - fmin(0.01, fmax(mu, 0.1 * p.tol_mu / mu));
+                const double al = (tmax > eta) ? eta / tmax : 1.0;
                 a += al * da; d += al * dd;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) { s[c] += al * dsa[c]; lam[c] += al * dla[c]; }
@@ -584,7 +586,7 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
             ++it;
         }
         iters = it;
-        if (converged) status = MPCB_ST_OPTIMAL;
+        if (converged || (feasible0 && res_d < 1e-8 * gscale && res_p < 1e-9 && mu < 1e-9)) status = MPCB_ST_OPTIMAL;
         else if (feasible0 && res_d < 1e-6 * gscale && res_p < 1e-7 && mu < 1e-7) status = MPCB_ST_INACCURATE;
         else { status = MPCB_ST_FAILED; solved = false; break; }
         solved = true;

@@ -192,7 +192,7 @@ class Condensed:
         return A, C
 
     # ---- Mehrotra predictor-corrector, the iteration the kernel runs
-    def solve(self, a0=None, d0=None, tol_mu=1e-12, tol_p=1e-10, tol_d=1e-9, max_iter=40, verbose=False):
+    def solve(self, a0=None, d0=None, tol_mu=1e-12, tol_p=1e-10, tol_d=1e-9, max_iter=40, verbose=False, eta_fn=None, init=None):
         """Stationarity test: |r_d| < tol_d + 1e-12 * (1 + |grad J(0)|_inf) (the gradient's rounding floor scales with it)."""
         T = self.T
         A, B, C = self.hessian()
@@ -203,6 +203,9 @@ class Condensed:
         d = np.zeros(T) if d0 is None else np.array(d0, float)
         s = np.where(msk, np.maximum(h - self.G_apply(a, d), 1.0), 1.0)
         lam = np.where(msk, 1.0, 0.0)
+        if init is not None:                       # experiment hook: (slack floor, mu0) -> centred start lam = mu0 / s
+            s = np.where(msk, np.maximum(h - self.G_apply(a, d), init[0]), 1.0)
+            lam = np.where(msk, init[1] / s, 0.0)
         m = msk.sum()
         status = 1
         g0a, g0d = self.grad(np.zeros(T), np.zeros(T))
@@ -250,7 +253,10 @@ class Condensed:
             mu_aff = float(((s + al * ds) * (lam + al * dl))[msk].sum()) / m
             sigma = (mu_aff / mu) ** 3
             da_, dd_, ds, dl = direction(s * lam + ds * dl - sigma * mu)
-            al = min(1.0, 0.99 * min(maxstep(s, ds), maxstep(lam, dl)))
+            # the kernel's adaptive fraction to the boundary (mpcb_step.cuh): 0.99 -> 1 as the gap closes, floored so that one
+            # step cannot push the gap far below its target
+            eta = (1.0 - min(0.01, max(mu, 0.1 * tol_mu / mu))) if eta_fn is None else eta_fn(mu)
+            al = min(1.0, eta * min(maxstep(s, ds), maxstep(lam, dl)))
             a, d, s, lam = a + al * da_, d + al * dd_, s + al * ds, lam + al * dl
         x, y, v, ph = self.states(a, d)
         return dict(oa=a, od=d, ox=x, oy=y, ov=v, oyaw=ph, iters=it, status=status)
