@@ -591,7 +591,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
             using SMg = WarpSmem<T>;
             double sa = g0a, sd = g0d;
             const double* const hbr = &sm.HB[SMg::colB(grow)];                   // hbr[j] = B(steer j, accel lane)
-#pragma unroll
+#pragma unroll 4
             for (int j = 0; j < T; ++j) {
                 const double aj = shfl(a, j), dj = shfl(d, j);
                 const int cj = SMg::colB(j) + grow;
@@ -769,7 +769,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
             const double* const LCr = &sm.LC[SM::colL(lrow)];
             const double* const LBr = &sm.LB[SM::colB(lrow)];        // LBr[k] = (steer row k, accel column lane)
             auto back_solve = [&](double ha, double hd, double& xa, double& xd) {      // L' x = h, h = D^-1 z
-#pragma unroll
+#pragma unroll 4
                 for (int k = T - 1; k >= 0; --k) {
                     const double xk = shfl(hd, k);
                     const double uc = LCr[k] * invd, ub = LBr[k] * inva;
@@ -777,7 +777,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                     ha = fma(-ub, xk, ha);
                 }
                 xd = hd;
-#pragma unroll
+#pragma unroll 4
                 for (int k = T - 1; k >= 1; --k) {
                     const double xk = shfl(ha, k);
                     const double ua = LAr[k] * inva;
@@ -789,7 +789,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                 const double* colA = &sm.LA[lrow];
                 const double* colB = &sm.LB[lrow];
                 double ga = fa * inva;
-#pragma unroll
+#pragma unroll 4
                 for (int k = 0; k < T; ++k) {
                     const double zk = shfl(ga, k);
                     const double ua = colA[SM::colL(k)] * inva, ub = colB[SM::colB(k)];
@@ -798,7 +798,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                 }
                 const double* colC = &sm.LC[lrow];
                 double gd = fd * invd;
-#pragma unroll
+#pragma unroll 4
                 for (int k = 0; k < T - 1; ++k) {
                     const double zk = shfl(gd, k);
                     const double uc = colC[SM::colL(k)] * invd;

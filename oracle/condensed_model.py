@@ -192,7 +192,7 @@ class Condensed:
         return A, C
 
     # ---- Mehrotra predictor-corrector, the iteration the kernel runs
-    def solve(self, a0=None, d0=None, tol_mu=1e-12, tol_p=1e-10, tol_d=1e-9, max_iter=40, verbose=False, eta_fn=None, init=None):
+    def solve(self, a0=None, d0=None, tol_mu=1e-12, tol_p=1e-10, tol_d=1e-9, max_iter=40, verbose=False, eta_fn=None, init=None, warm=None):
         """Stationarity test: |r_d| < tol_d + 1e-12 * (1 + |grad J(0)|_inf) (the gradient's rounding floor scales with it)."""
         T = self.T
         A, B, C = self.hessian()
@@ -206,6 +206,10 @@ class Condensed:
         if init is not None:                       # experiment hook: (slack floor, mu0) -> centred start lam = mu0 / s
             s = np.where(msk, np.maximum(h - self.G_apply(a, d), init[0]), 1.0)
             lam = np.where(msk, init[1] / s, 0.0)
+        if warm is not None:                       # experiment hook: (lam_prev [8,T] or like, delta_s, delta_l)
+            lp, ds_, dl_ = warm
+            s = np.where(msk, np.maximum(h - self.G_apply(a, d), ds_), 1.0)
+            lam = np.where(msk, np.maximum(lp, dl_), 0.0)
         m = msk.sum()
         status = 1
         g0a, g0d = self.grad(np.zeros(T), np.zeros(T))
@@ -259,4 +263,4 @@ class Condensed:
             al = min(1.0, eta * min(maxstep(s, ds), maxstep(lam, dl)))
             a, d, s, lam = a + al * da_, d + al * dd_, s + al * ds, lam + al * dl
         x, y, v, ph = self.states(a, d)
-        return dict(oa=a, od=d, ox=x, oy=y, ov=v, oyaw=ph, iters=it, status=status)
+        return dict(oa=a, od=d, ox=x, oy=y, ov=v, oyaw=ph, iters=it, status=status, s=s, lam=lam)
