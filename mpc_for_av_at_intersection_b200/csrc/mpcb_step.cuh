@@ -807,65 +807,59 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                 fa = ga; fd = gd;                              // = D^-1 L^-1 r
             };
 
-            // ---- predictor ---------------------------------------------------------------------------------
-            double dsa[8], dla[8];
-            double sigma_mu;
-            {
+            // ---- predictor (ph = 0) and corrector (ph = 1): one copy of the back solve, the G product and the ratio test ----
+            // (a rolled two-pass loop: the hot loop body must stay inside the 32 KB instruction cache)
+            double dsa[8], dla[8], rc[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) { rc[c] = mk[c] ? s[c] * lam[c] : 0.0; dsa[c] = 0.0; dla[c] = 0.0; }
+#pragma unroll 1
+            for (int ph = 0; ph < 2; ++ph) {
+                double ha, hd;
+                if (ph == 0) { ha = ra * inva; hd = rdl * invd; }              // inva = invd = 0 on the idle lanes
+                else {
+                    double y[8], ya, yd;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) y[c] = rc[c] * sinv[c] - w[c] * rp[c];
+                    GT_apply<T>(y, dt, lane, ya, yd);
+                    ha = ya - rda; hd = yd - rdd;
+                    fwd_solve(ha, hd);
+                }
                 double da, dd, g[8];
-                back_solve(ra * inva, rdl * invd, da, dd);                   // inva = invd = 0 on the idle lanes
+                back_solve(ha, hd, da, dd);
                 G_apply<T>(da, dd, dt, lane, g);
                 double tmax = 0.0;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
-                    dla[c] = mk[c] ? -lam[c] - w[c] * dsa[c] : 0.0;
+                    dla[c] = mk[c] ? -(rc[c] + lam[c] * dsa[c]) * sinv[c] : 0.0;   // rc = s lam in the predictor: -lam - w ds
                     const double linv = mk[c] ? rcp(lam[c]) : 0.0;
                     tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
                 }
                 tmax = warp_max(tmax);
-                const double al = 1.0 / fmax(1.0, tmax);
-                double sl = 0.0;
+                if (ph == 0) {
+                    const double al = 1.0 / fmax(1.0, tmax);
+                    double sl = 0.0;
 #pragma unroll
-                for (int c = 0; c < 8; ++c) sl += (s[c] + al * dsa[c]) * (lam[c] + al * dla[c]);
-                const double mu_aff = warp_sum(sl) / m_cnt;
-                const double r = mu_aff / mu;
-                sigma_mu = r * r * r * mu;
-            }
-            // ---- corrector ---------------------------------------------------------------------------------
-            {
-                double rc[8], y[8], ya, yd;
+                    for (int c = 0; c < 8; ++c) sl += (s[c] + al * dsa[c]) * (lam[c] + al * dla[c]);
+                    const double mu_aff = warp_sum(sl) / m_cnt;
+                    const double r = mu_aff / mu;
+                    const double sigma_mu = r * r * r * mu;
 #pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    rc[c] = mk[c] ? s[c] * lam[c] + dsa[c] * dla[c] - sigma_mu : 0.0;
-                    y[c] = rc[c] * sinv[c] - w[c] * rp[c];
+                    for (int c = 0; c < 8; ++c) rc[c] = mk[c] ? s[c] * lam[c] + dsa[c] * dla[c] - sigma_mu : 0.0;
+                } else {
+                    // Fraction to the boundary: 0.99 while the gap is large, -> 1 as it closes (Mehrotra's adaptive rule).  With a
+                    // fixed 0.99 every residual and the gap shrink by exactly 100x per iteration in the end game (linear); with
+                    // 1 - mu the end game is quadratic: 2 iterations instead of 4-5 from mu = 1e-4 to 1e-12.  The floor
+                    // 0.1 tol_mu / mu keeps one step from driving the gap far below its target (slacks of 1e-20 wreck the
+                    // conditioning of H + G'WG while the residuals still need a step).
+                    const double eta = 1.0 - fmin(0.01, fmax(mu, 0.1 * p.tol_mu / mu));
+                    const double al = (tmax > eta) ? eta / tmax : 1.0;
+                    a += al * da; d += al * dd;
+                    const double om = 1.0 - al;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) { s[c] += al * dsa[c]; lam[c] += al * dla[c]; rp[c] *= om; }
+                    rda *= om; rdd *= om; res_d *= om; res_p *= om;
                 }
-                GT_apply<T>(y, dt, lane, ya, yd);
-                double fa = ya - rda, fd = yd - rdd;
-                fwd_solve(fa, fd);
-                double da, dd, g[8];
-                back_solve(fa, fd, da, dd);
-                G_apply<T>(da, dd, dt, lane, g);
-                double tmax = 0.0;
-#pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
-                    dla[c] = mk[c] ? -(rc[c] + lam[c] * dsa[c]) * sinv[c] : 0.0;
-                    const double linv = mk[c] ? rcp(lam[c]) : 0.0;
-                    tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
-                }
-                tmax = warp_max(tmax);
-                // Fraction to the boundary: 0.99 while the gap is large, -> 1 as it closes (Mehrotra's adaptive rule).  With a
-                // fixed 0.99 every residual and the gap shrink by exactly 100x per iteration in the end game (linear); with
-                // 1 - mu the end game is quadratic: 2 iterations instead of 4-5 from mu = 1e-4 to 1e-12.  The floor
-                // 0.1 tol_mu / mu keeps one step from driving the gap far below its target (slacks of 1e-20 wreck the
-                // conditioning of H + G'WG while the residuals still need a step).
-                const double eta = 1.0 - fmin(0.01, fmax(mu, 0.1 * p.tol_mu / mu));
-                const double al = (tmax > eta) ? eta / tmax : 1.0;
-                a += al * da; d += al * dd;
-                const double om = 1.0 - al;
-#pragma unroll
-                for (int c = 0; c < 8; ++c) { s[c] += al * dsa[c]; lam[c] += al * dla[c]; rp[c] *= om; }
-                rda *= om; rdd *= om; res_d *= om; res_p *= om;
             }
             ++it;
             verified = false;
