@@ -603,6 +603,8 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
         double res_d = 1e300, res_p = 1e300, mu = 1e300;
         bool converged = false, broke = false;
         int it = 0;
+        double mu_prev = 1e300;
+        bool eta_safe = false;
         // Residual bookkeeping.  A Newton step of length al scales BOTH linear residuals by (1 - al): r_p exactly (the
         // slack step is defined from it), r_d up to the backward error of the LDL' solve.  The loop therefore carries
         // the residuals forward by that factor and re-evaluates them from scratch (Hessian mat-vec, G and G' scans)
@@ -852,7 +854,11 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                     // 1 - mu the end game is quadratic: 2 iterations instead of 4-5 from mu = 1e-4 to 1e-12.  The floor
                     // 0.1 tol_mu / mu keeps one step from driving the gap far below its target (slacks of 1e-20 wreck the
                     // conditioning of H + G'WG while the residuals still need a step).
-                    const double eta = 1.0 - fmin(0.01, fmax(mu, 0.1 * p.tol_mu / mu));
+                    // safeguard: an aggressive step that left the iterate badly centred shows as a gap that fails to halve; from then
+                    // on the classic 0.99 (3 solves in 1.3 M stalled without it, profiles/r01g_NOTES.md)
+                    if (mu_prev < 0.01 && mu > 0.5 * mu_prev) eta_safe = true;
+                    mu_prev = mu;
+                    const double eta = eta_safe ? 0.99 : 1.0 - fmin(0.01, fmax(mu, 0.1 * p.tol_mu / mu));
                     const double al = (tmax > eta) ? eta / tmax : 1.0;
                     a += al * da; d += al * dd;
                     const double om = 1.0 - al;

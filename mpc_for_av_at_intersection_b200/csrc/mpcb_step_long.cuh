@@ -413,6 +413,8 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
         double res_d = 1e300, res_p = 1e300, mu = 1e300;
         bool converged = false;
         int it = 0;
+        double mu_prev = 1e300;
+        bool eta_safe = false;
         while (feasible0) {
             double rda, rdd, rp[8];
             {
@@ -577,7 +579,11 @@ __global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, c
                 }
                 tmax = bo.max(tmax);
                 // adaptive fraction to the boundary, see mpcb_step.cuh
-                const double eta = 1.0 - fmin(0.01, fmax(mu, 0.1 * p.tol_mu / mu));
+                // safeguard: an aggressive step that left the iterate badly centred shows as a gap that fails to halve; from then
+                // on the classic 0.99 (3 solves in 1.3 M stalled without it, profiles/r01g_NOTES.md)
+                if (mu_prev < 0.01 && mu > 0.5 * mu_prev) eta_safe = true;
+                mu_prev = mu;
+                const double eta = eta_safe ? 0.99 : 1.0 - fmin(0.01, fmax(mu, 0.1 * p.tol_mu / mu));
                 const double al = (tmax > eta) ? eta / tmax : 1.0;
                 a += al * da; d += al * dd;
 #pragma unroll

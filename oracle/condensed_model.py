@@ -214,6 +214,7 @@ class Condensed:
         status = 1
         g0a, g0d = self.grad(np.zeros(T), np.zeros(T))
         gscale = 1.0 + max(np.abs(g0a).max(), np.abs(g0d).max())
+        mu_prev, eta_safe = 1e300, False
         for it in range(1, max_iter + 1):
             ga, gd = self.grad(a, d)
             gta, gtd = self.GT_apply(lam)
@@ -258,8 +259,14 @@ class Condensed:
             sigma = (mu_aff / mu) ** 3
             da_, dd_, ds, dl = direction(s * lam + ds * dl - sigma * mu)
             # the kernel's adaptive fraction to the boundary (mpcb_step.cuh): 0.99 -> 1 as the gap closes, floored so that one
-            # step cannot push the gap far below its target
-            eta = (1.0 - min(0.01, max(mu, 0.1 * tol_mu / mu))) if eta_fn is None else eta_fn(mu)
+            # step cannot push the gap far below its target; back to 0.99 for good once an aggressive step failed to halve the gap
+            if eta_fn is None:
+                if mu_prev < 0.01 and mu > 0.5 * mu_prev:
+                    eta_safe = True
+                mu_prev = mu
+                eta = 0.99 if eta_safe else 1.0 - min(0.01, max(mu, 0.1 * tol_mu / mu))
+            else:
+                eta = eta_fn(mu)
             al = min(1.0, eta * min(maxstep(s, ds), maxstep(lam, dl)))
             a, d, s, lam = a + al * da_, d + al * dd_, s + al * ds, lam + al * dl
         x, y, v, ph = self.states(a, d)
