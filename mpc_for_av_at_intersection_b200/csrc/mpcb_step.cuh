@@ -101,7 +101,7 @@ __device__ __forceinline__ void ldl_accel_steps(WarpSmem<T>& sm, double (&R)[T],
         ra = fma(-a0s, zk, ra);
         rdl = fma(-b0, zk, rdl);
         R[0] = R[1] - la * c[1];
-        a0 = R[0] + wv_suf + (lane == k + 1 ? dA : 0.0);           // G'WG terms join when the column is published
+        a0 = R[0] + (lane == k + 1 ? dA : 0.0);                    // the diagonal G'WG term joins when the column is published
         ivm = rcp(a0);
         Q[0] = Q[1] - lb * c[1];
 #pragma unroll
@@ -137,7 +137,7 @@ __device__ __forceinline__ void ldl_steer_steps(WarpSmem<T>& sm, double (&C)[T],
         const double lc = c0s * iv;
         rdl = fma(-c0s, zk, rdl);
         C[0] = C[1] - lc * c[1];
-        c0 = C[0] + (lane == k + 1 ? dC : 0.0) - (lane == k + 2 ? wr_prev : 0.0);
+        c0 = C[0];                                                  // the G'WG terms are already in the window (added to the scratch)
         ivm = rcp(c0);
 #pragma unroll
         for (int j = 2; j <= JMAX; ++j) C[j - 1] = C[j] - lc * c[j];
@@ -681,10 +681,10 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                 double R[T], Q[T];                               // accel-block row and cross-block row of this lane
 #pragma unroll
                 for (int j = 0; j < T; ++j) {                    // idle lanes read valid memory, their rows are never used
-                    R[j] = sm.HA[SM::colB(j) + lane];
+                    R[j] = sm.HA[SM::colB(j) + lane] + wv_suf;   // dt^2 L'WL: entry (i, j <= i) is this lane's suffix sum
                     Q[j] = sm.HB[SM::colB(j) + lane];
                 }
-                double a0 = R[0] + wv_suf + (lane == 0 ? dA : 0.0);
+                double a0 = R[0] + (lane == 0 ? dA : 0.0);
                 double ivm = rcp(a0);
                 __syncwarp();
                 constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
@@ -739,6 +739,13 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                         }
                 }
                 __syncwarp();
+                // G'WG of the steer block (diagonal dC, sub-diagonal -wr_prev) goes into this lane's row of the scratch, i.e.
+                // into the window before the elimination starts instead of onto the pivot-to-pivot chain of every step
+                if (act) {
+                    double* Sw = &sm.LC[lane * SM::SB];
+                    Sw[lane] += dC;
+                    if (lane >= 1) Sw[lane - 1] -= wr_prev;
+                }
                 double C[T];
                 {
                     const double* Sr = &sm.LC[(act ? lane : 0) * SM::SB];
@@ -751,7 +758,7 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                     if (T & 1) C[T - 1] = sm.HC[SM::colB(T - 1) + lane] + Sr[T - 1];
                 }
                 __syncwarp();                                              // the scratch is overwritten by the factor below
-                double c0 = C[0] + (lane == 0 ? dC : 0.0) - (lane == 1 ? wr_prev : 0.0);
+                double c0 = C[0];
                 double ivm = rcp(c0);
                 constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
                 ldl_steer_steps<T, T - 1>(sm, C, 0, K1, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
