@@ -84,8 +84,6 @@ __device__ __forceinline__ void ldl_accel_steps(WarpSmem<T>& sm, double (&R)[T],
         // rewrites (or into the pad after the last column); lanes other than k write their own scratch slot
         sm.LA[col + lane] = a0s; sm.LB[SM::colB(k) + lane] = b0;
         sts_pair_if(mine, &sm.iz[k].x, ivm, ra * ivm);
-        inva = mine ? ivm : inva;
-        bad = bad || (mine && !(a0 > 0.0));
         __syncwarp();
         const double* pc = &sm.LA[col + k];
         const double2 izk = sm.iz[k];
@@ -121,8 +119,6 @@ __device__ __forceinline__ void ldl_steer_steps(WarpSmem<T>& sm, double (&C)[T],
         const double c0s = lane > k ? c0 : 0.0;
         sm.LC[col + lane] = c0s;
         sts_pair_if(mine, &sm.iz[T + k].x, ivm, rdl * ivm);
-        invd = mine ? ivm : invd;
-        bad = bad || (mine && !(c0 > 0.0));
         __syncwarp();
         const double* pc = &sm.LC[col + k];
         const double2 izk = sm.iz[T + k];
@@ -767,6 +763,13 @@ __device__ __forceinline__ void mpc_step_body(const StepParams& p) {
                 ldl_steer_steps<T, T - 1 - K3>(sm, C, K3, T, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
             }
             __syncwarp();
+            // every lane's own pivot reciprocals come back from the published {1/d, z} pairs (one load each instead of a
+            // select per elimination step); a pivot that was not positive and finite shows in its reciprocal
+#ifndef MPCB_BLOCKED_ACCEL
+            inva = act ? sm.iz[lane].x : 0.0;
+#endif
+            invd = act ? sm.iz[T + lane].x : 0.0;
+            bad = bad || (act && !(inva > 0.0 && inva < 1e300 && invd > 0.0 && invd < 1e300));
             if (__any_sync(MPCB_FULL, bad)) { broke = true; break; }
             if (!act) { ra = 0.0; rdl = 0.0; }
             // Triangular solves with the pivots in rolled loops.  The factor blocks are zero on and above the diagonal,
