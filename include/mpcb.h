@@ -261,6 +261,9 @@ int mpcb_session_scripted_loop_dev(mpcb_handle* h, int nsteps, double* history_d
 #define MPCB_F_SCRIPT 18    /* double [B,MPCB_MAX_OBSTACLES,8] xc, yc, theta, counter, direction, turning, speed, offset */
 #define MPCB_F_OBS 19       /* double [B,MPCB_MAX_OBSTACLES,6] last get() rows (when no obs_history_dev was given) */
 #define MPCB_F_NOBS 20      /* int    [B] scripted obstacles per ego */
+#define MPCB_F_LAUNCH_ORDER 21 /* int [B] launch slot -> problem of the next step: longest-first by the interior-point
+                                 iterations of the last step (a permutation; identity until the first step and whenever the
+                                 batch is under one or over a dozen waves of resident warps).  No effect on any result. */
 
 /* ---- motion-primitive A* planner ------------------------------------------------------
  * replaces: `MotionPrimitiveSearch(scenario, car_dimensions, mps, margin).run()` (main/lib/motion_primitive_search_modified.py:

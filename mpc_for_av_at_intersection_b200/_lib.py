@@ -46,7 +46,7 @@ EXPORTS = [
 ]
 
 F_STATE, F_OA, F_OD, F_TRAJ, F_XREF, F_DI_AI, F_XDEV, F_TARGET, F_WARM, F_STATUS, F_ITERS, F_DONE, F_NCOURSE, \
-    F_ROUTE, F_GOAL, F_AGENT_IDX, F_COLLIDED, F_COLL_IDX, F_SCRIPT, F_OBS, F_NOBS = range(21)
+    F_ROUTE, F_GOAL, F_AGENT_IDX, F_COLLIDED, F_COLL_IDX, F_SCRIPT, F_OBS, F_NOBS, F_LAUNCH_ORDER = range(22)
 MAX_OBSTACLES = 8
 
 

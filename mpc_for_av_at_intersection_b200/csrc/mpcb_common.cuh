@@ -42,6 +42,11 @@ struct StepParams {
                              //   main/lib/mpc_sensitivity.py:150-158 re-reads its JSON on every solve
     const int* vcut;         // [B] or null: main/lib/mpc_with_speed.py:276-282 cutoff_idx (cv[cutoff_idx:] = 0)
     double ref_speed;        // cv elsewhere (mpc_with_speed.py:36,280: 25/3.6); xref[2,t] = cv[idx_t] (:104)
+    // longest-first launch order for the next control step (resident sessions only; all null = launch slot i solves problem i)
+    int* lpt_order;          // [B] io: slot -> problem of THIS launch; rewritten by the last warp to finish, sorted by the
+                             //   interior-point iterations each problem just needed (a good predictor of the next step's)
+    int* lpt_rank;           // [B] scratch: (bin << 24) | rank inside the bin
+    int* lpt_hist;           // [65] scratch: 64 bins (bin 0 = most iterations) + the finished-warp counter; zero between launches
 };
 
 namespace mpcb {

@@ -36,6 +36,7 @@ _FIELDS = {
     "script": (_lib.F_SCRIPT, np.float64, lambda T: (_lib.MAX_OBSTACLES, 8)),
     "obstacles": (_lib.F_OBS, np.float64, lambda T: (_lib.MAX_OBSTACLES, 6)),
     "n_obstacles": (_lib.F_NOBS, np.int32, lambda T: ()),
+    "launch_order": (_lib.F_LAUNCH_ORDER, np.int32, lambda T: ()),
 }
 
 

@@ -133,3 +133,33 @@ def test_closed_loop_sweep_chunks_and_shards():
         assert np.array_equal(one[k], np.concatenate([h[k] for h in halves])), k
     assert one["history"].shape == (300, 12, 8) and (one["fail_count"] == 0).all()
     assert np.isfinite(one["final_state"]).all()
+
+
+def test_longest_first_launch_order_changes_nothing():
+    """Above one wave of resident warps the session launches the problems longest-first (by the interior-point iterations
+    of the previous step; the table is rebuilt by the last warp of every launch).  The table must be a permutation sorted
+    by those iterations, and every per-problem result must be bit-identical to the same problems run in sessions small
+    enough to keep the identity order."""
+    from mpc_for_av_at_intersection_b200.scenarios import make_workload
+    T, B, K = 20, 3000, 6
+    ses, cfg, cs = _session(T, B)
+    wl = make_workload(cs, B, seed=77)
+    ses.begin(wl["route"], target_ind=wl["target_ind"])
+    ses.store("state", wl["state"])
+    assert np.array_equal(ses.fetch("launch_order"), np.arange(B))
+    for k in range(K):
+        ses.closed_loop_dev(1, 0, 0, goal_test=False)
+        order, it = ses.fetch("launch_order"), ses.fetch("iters")
+        assert np.array_equal(np.sort(order), np.arange(B)), "the launch table must stay a permutation"
+        assert (np.diff(it[order]) <= 0).all(), "longest first"
+    big = {n: ses.fetch(n) for n in ("state", "oa", "odelta", "di_ai", "target_ind", "iters", "status")}
+    assert big["iters"].max() > big["iters"].min() + 3
+    small, _, _ = _session(T, 1000)
+    for c0 in range(0, B, 1000):
+        sl = slice(c0, c0 + 1000)
+        small.begin(wl["route"][sl], target_ind=wl["target_ind"][sl])
+        small.store("state", wl["state"][sl])
+        small.closed_loop_dev(K, 0, 0, goal_test=False)
+        assert np.array_equal(small.fetch("launch_order"), np.arange(1000)), "under one wave the order stays the identity"
+        for n in big:
+            assert np.array_equal(small.fetch(n), big[n][sl]), n
