@@ -170,12 +170,13 @@ int launch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
 
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st);
 
-// long horizons (mpcb_step_long.cuh): one CTA of kLongThreads per problem, system matrix in shared memory
-int launch_step_long(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
+// long horizons (mpcb_step_long.cuh): one CTA per problem, system matrix in shared memory
+template <int NT, int MINB = 1>
+int launch_step_long_nt(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     const int T = h->cfg.T;
-    if (T + 1 > kLongThreads) { h->err = "mpcb: horizon too long for the CTA-per-problem kernel"; return MPCB_EINVAL; }
-    const size_t smem = mpcb::LongSmem::bytes(T, kLongThreads);
-    auto kern = mpcb::mpc_step_long_kernel<kLongThreads>;
+    if (T + 1 > NT) { h->err = "mpcb: horizon too long for the CTA-per-problem kernel"; return MPCB_EINVAL; }
+    const size_t smem = mpcb::LongSmem::bytes(T, NT);
+    auto kern = mpcb::mpc_step_long_kernel<NT, MINB>;
     static thread_local int configured_dev = -1;
     static thread_local size_t configured_smem = 0;
     if (configured_dev != h->device || configured_smem < smem) {
@@ -183,10 +184,19 @@ int launch_step_long(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         configured_dev = h->device; configured_smem = smem;
     }
-    kern<<<p.B, kLongThreads, smem, st>>>(p, T);
+    kern<<<p.B, NT, smem, st>>>(p, T);
     CUDA_TRY(h, cudaGetLastError());
     h->launches++;
     return MPCB_OK;
+}
+// Threads per problem: T = 80 (122 KB of shared memory: one CTA per SM whatever its size) runs 61 % faster with 8 warps
+// sharing the rows of the trailing update than with 4 (29.0 K vs 18.0 K solves/s at B = 4096); T = 40 (30 KB, two
+// 248-register CTAs per SM either way) is faster with 4 (157 K vs 118 K).  Also measured and rejected: 512 threads at 128
+// registers (spills; 27.0 K at T = 80), register caps for 3 or 4 CTAs per SM at T = 40 (135 K / 162 K with spills).
+int launch_step_long(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
+    static const int nt_env = getenv("MPCB_LONG_THREADS") ? atoi(getenv("MPCB_LONG_THREADS")) : 0;
+    const bool wide = nt_env ? nt_env == 256 : h->cfg.T > 40;
+    return wide ? launch_step_long_nt<256>(h, p, st) : launch_step_long_nt<kLongThreads>(h, p, st);
 }
 
 StepParams make_params(const mpcb_handle* h) {

@@ -178,8 +178,8 @@ struct LongSmem {
 enum { LT_OA = 0, LT_TERM, LT_ZX, LT_ZY, LT_WX, LT_WY, LT_BB, LT_HH, LT_GAX, LT_GAY, LT_GCX, LT_GCY, LT_HA, LT_HC, LT_HB,
        LT_DGA, LT_DGC, LT_WVS, LT_DA, LT_DC, LT_WRP, LT_U0, LT_U1, LT_SPARE };
 
-template <int NT>
-__global__ void __launch_bounds__(NT) mpc_step_long_kernel(const StepParams p, const int T) {
+template <int NT, int MINB = 1>
+__global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParams p, const int T) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int b = blockIdx.x;
     if (b >= p.B) return;
