@@ -516,8 +516,9 @@ int session_alloc(mpcb_handle* h) {
     auto put = [&](size_t bytes) { size_t at = o; o = align256(o + bytes); return at; };
     const size_t o_state = put(8 * 4 * B), o_L = put(8 * B), o_oa = put(8 * T * B), o_od = put(8 * T * B),
                  o_traj = put(8 * 4 * (T + 1) * B), o_xref = put(8 * 4 * (T + 1) * B), o_diai = put(8 * 2 * B),
+                 o_status = put(4 * B),      // right behind di_ai: the host-buffer step fetches both with ONE copy
                  o_xdev = put(8 * B), o_goal = put(8 * 2 * B), o_route = put(4 * B), o_nc = put(4 * B),
-                 o_tgt = put(4 * B), o_warm = put(4 * B), o_status = put(4 * B), o_iters = put(4 * B),
+                 o_tgt = put(4 * B), o_warm = put(4 * B), o_iters = put(4 * B),
                  o_done = put(4 * B), o_aidx = put(4 * B), o_coll = put(4 * B), o_cidx = put(4 * B),
                  o_nscr = put(4 * B), o_script = put(8 * 8 * MPCB_CP_MAX_OBS * B), o_obs = put(8 * 6 * MPCB_CP_MAX_OBS * B),
                  o_pw = put(8 * 12 * B), o_vcut = put(4 * B), o_lord = put(4 * B), o_lrank = put(4 * B), o_lhist = put(4 * 65);
@@ -651,8 +652,13 @@ int mpcb_session_step_host(mpcb_handle* h, const double* state_host, double* di_
     CUDA_TRY(h, cudaMemcpyAsync(s.state, s.pin + s.pin_state, 32 * B, cudaMemcpyHostToDevice, st));
     int rc = dispatch_step(h, session_params(h), st);
     if (rc != MPCB_OK) return rc;
-    CUDA_TRY(h, cudaMemcpyAsync(s.pin + s.pin_diai, s.di_ai, 16 * B, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(h, cudaMemcpyAsync(s.pin + s.pin_status, s.status, 4 * B, cudaMemcpyDeviceToHost, st));
+    if ((char*)s.status - (char*)s.di_ai == (ptrdiff_t)(s.pin_status - s.pin_diai) && s.pin_status - s.pin_diai < 16 * B + 256) {
+        // full batch: di_ai and status are neighbours in the slab and in the pinned buffer -- one copy, one DMA latency
+        CUDA_TRY(h, cudaMemcpyAsync(s.pin + s.pin_diai, s.di_ai, (s.pin_status - s.pin_diai) + 4 * B, cudaMemcpyDeviceToHost, st));
+    } else {
+        CUDA_TRY(h, cudaMemcpyAsync(s.pin + s.pin_diai, s.di_ai, 16 * B, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(h, cudaMemcpyAsync(s.pin + s.pin_status, s.status, 4 * B, cudaMemcpyDeviceToHost, st));
+    }
     CUDA_TRY(h, cudaStreamSynchronize(st));
     memcpy(di_ai_host, s.pin + s.pin_diai, 16 * B);
     if (status_host) memcpy(status_host, s.pin + s.pin_status, 4 * B);
