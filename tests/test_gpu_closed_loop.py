@@ -163,3 +163,32 @@ def test_longest_first_launch_order_changes_nothing():
         assert np.array_equal(small.fetch("launch_order"), np.arange(1000)), "under one wave the order stays the identity"
         for n in big:
             assert np.array_equal(small.fetch(n), big[n][sl]), n
+
+
+def test_device_history_to_reference_history_objects():
+    """SURVEY 8f N4 on the device path: the [steps, B, 8] block written by the closed-loop kernel, turned into the
+    reference's per-vehicle `History` (results.histories_from_device), against the History the unmodified reference
+    accumulated for the same loops (golden): same length, time stamps, and columns within the closed-loop tolerances."""
+    import torch
+    from mpc_for_av_at_intersection_b200 import results
+    T = 13
+    g = golden(f"closed_loop_T{T}.npz")
+    sel, route, nsteps, hist = _loops(g)
+    keep = [i for i in range(len(sel)) if int(route[i]) not in SENSITIVE_ROUTES]
+    B = len(keep)
+    ses, cfg, cs = _session(T, B)
+    ses.begin(route[keep])
+    state0 = np.stack([hist[i][0, :4] for i in keep])
+    ses.store("state", state0)
+    K = int(nsteps.max()) + 2
+    H = torch.full((K, B, 8), float("nan"), dtype=torch.float64, device="cuda")
+    ses.closed_loop_dev(K, H.data_ptr(), 0)
+    torch.cuda.synchronize()
+    hs = results.histories_from_device(H.cpu().numpy(), state0, 0.2)
+    for j, i in enumerate(keep):
+        tab = results.history_table(hs[j])                     # x y yaw v t delta a xref_deviation
+        ref = hist[i]                                          # x y yaw v delta a xref_deviation
+        assert tab.shape[0] == ref.shape[0], (tab.shape, ref.shape)
+        assert np.allclose(tab[:, 4], 0.2 * np.arange(1, len(tab) + 1))
+        assert np.abs(tab[:, [0, 1, 2, 3, 5, 6]] - ref[:, :6]).max() < 1e-6
+        assert np.nanmax(np.abs(tab[1:, 7] - ref[1:, 6])) < 1e-6

@@ -100,3 +100,16 @@ def test_planner_facade_feeds_the_mpc():
     with pytest.raises(Exception, match="No solution found"):
         bad = dataclasses.replace(planner.intersection(start_pos=3, turn_indicator=1), start=tuple(g["start"][np.flatnonzero(g["failed"])[0]]))
         planner.MotionPrimitiveSearch(bad, car, mps, margin=car.radius).run()
+
+
+def test_capacity_overflow_is_reported_not_silent():
+    """A search that needs more open-list or closed-set entries than it was given must come back as PLAN_OVERFLOW (with no
+    path), never as a wrong path; the same search with room succeeds."""
+    planner, g, lib = _setup()
+    k = int(np.argmax(g["n_expanded"] * (g["failed"] == 0)))          # the longest recorded search
+    sc = dataclasses.replace(planner.intersection(turn_indicator=int(g["turn"][k]), start_pos=int(g["start_pos"][k])),
+                             start=tuple(g["start"][k]))
+    small = planner.plan_batch([sc], lib, margin=float(g["radius"]), max_open=512, max_closed=256)
+    assert small.status[0] == planner.PLAN_OVERFLOW and small.n_path[0] == 0 and (small.mp_seq[0] == -1).all() and np.isnan(small.cost[0])
+    ok = planner.plan_batch([sc], lib, margin=float(g["radius"]))
+    assert ok.status[0] == planner.PLAN_OK and ok.cost[0] == g["cost"][k]
