@@ -682,11 +682,12 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 double a0 = R[0] + (lane == 0 ? dA : 0.0);
                 double ivm = rcp(a0);
                 __syncwarp();
-                constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
+                // three window sizes (measured: 2 segments 8.02 M solves/s, 3: 8.14, 4: 8.12, 6: 8.10 at B = 4096 -- wasted FMAs on
+                // dead columns against bytes of hot-loop code)
+                constexpr int K1 = T / 3, K2 = (2 * T) / 3;
                 ldl_accel_steps<T, T - 1>(sm, R, Q, 0, K1, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
                 ldl_accel_steps<T, T - 1 - K1>(sm, R, Q, K1, K2, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
-                ldl_accel_steps<T, T - 1 - K2>(sm, R, Q, K2, K3, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
-                ldl_accel_steps<T, T - 1 - K3>(sm, R, Q, K3, T, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
+                ldl_accel_steps<T, T - 1 - K2>(sm, R, Q, K2, T, lane, wv_suf, dA, ra, rdl, bad, inva, a0, ivm);
 #endif
             }
             {
@@ -755,11 +756,10 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 __syncwarp();                                              // the scratch is overwritten by the factor below
                 double c0 = C[0];
                 double ivm = rcp(c0);
-                constexpr int K1 = T / 4, K2 = T / 2, K3 = (3 * T) / 4;
+                constexpr int K1 = T / 3, K2 = (2 * T) / 3;
                 ldl_steer_steps<T, T - 1>(sm, C, 0, K1, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
                 ldl_steer_steps<T, T - 1 - K1>(sm, C, K1, K2, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
-                ldl_steer_steps<T, T - 1 - K2>(sm, C, K2, K3, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
-                ldl_steer_steps<T, T - 1 - K3>(sm, C, K3, T, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
+                ldl_steer_steps<T, T - 1 - K2>(sm, C, K2, T, lane, act, dC, wr_prev, rdl, bad, invd, c0, ivm);
             }
             __syncwarp();
             // every lane's own pivot reciprocals come back from the published {1/d, z} pairs (one load each instead of a
