@@ -126,6 +126,25 @@ int mpcb_step(mpcb_handle* h, int B, const double* state_dev, const int* route_d
               double* traj_dev, double* xref_dev, double* di_ai_dev, double* xdev_dev, int* status_dev,
               int* iters_dev, void* stream);
 
+/* ---- allocation-free step ---------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, results and
+ * asynchronous behaviour as mpcb_step, plus the longest-first launch order that otherwise needs a session: the order's
+ * scratch (iteration histogram, per-problem ranks, slot -> problem table) lives in a file-scope static __device__ array of
+ * 129 KB that every GPU loading the library holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine); the first call on a device looks the array's address up (cudaGetSymbolAddress), so make
+ * that first call outside a capture.
+ *   - B > MPCB_STATIC_MAX_BATCH (or > the handle's max_batch) and horizons T > 31 (their kernel has no scratch) are
+ *     rejected with MPCB_EINVAL and a message; use mpcb_step there.
+ *   - All calls on a device share the array, whatever the handle.  It keeps the last call's slot -> problem table (reset
+ *     when B changes; the histogram is cleared by every call); the table never changes a result, only the launch order.
+ *   - Calls that overlap on the GPU (two streams, two handles, two threads) race on the array: serialise them. */
+#define MPCB_STATIC_MAX_BATCH 16384
+int mpcb_step_static(mpcb_handle* h, int B, const double* state_dev, const int* route_dev, const int* ncourse_dev,
+                     const double* L_dev, int* target_ind_dev, int* warm_dev, double* oa_dev, double* od_dev,
+                     double* traj_dev, double* xref_dev, double* di_ai_dev, double* xdev_dev, int* status_dev,
+                     int* iters_dev, void* stream);
+
 /* Same call with HOST buffers (any pointer except state/route/ncourse may be NULL to skip that
  * output; in/out arrays are read and written).  Synchronous. */
 int mpcb_step_host(mpcb_handle* h, int B, const double* state, const int* route, const int* ncourse,

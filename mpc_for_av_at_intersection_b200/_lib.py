@@ -42,12 +42,13 @@ EXPORTS = [
     "mpcb_coupling", "mpcb_coupling_host", "mpcb_session_multi_agent_dev",
     "mpcb_session_set_scripted_host", "mpcb_session_scripted_loop_dev",
     "mpcb_session_set_weights_host", "mpcb_session_set_speed_cutoff_host",
-    "mpcb_plan_routes_host", "mpcb_plan_last_error",
+    "mpcb_plan_routes_host", "mpcb_plan_last_error", "mpcb_step_static",
 ]
 
 F_STATE, F_OA, F_OD, F_TRAJ, F_XREF, F_DI_AI, F_XDEV, F_TARGET, F_WARM, F_STATUS, F_ITERS, F_DONE, F_NCOURSE, \
     F_ROUTE, F_GOAL, F_AGENT_IDX, F_COLLIDED, F_COLL_IDX, F_SCRIPT, F_OBS, F_NOBS, F_LAUNCH_ORDER = range(22)
 MAX_OBSTACLES = 8
+STATIC_MAX_BATCH = 16384
 
 
 def build(verbose=False):
@@ -97,6 +98,8 @@ def lib():
     L.mpcb_set_courses_host.restype = C.c_int
     L.mpcb_step.argtypes = [vp, C.c_int] + [vp] * 15
     L.mpcb_step.restype = C.c_int
+    L.mpcb_step_static.argtypes = [vp, C.c_int] + [vp] * 15
+    L.mpcb_step_static.restype = C.c_int
     L.mpcb_step_host.argtypes = [vp, C.c_int] + [vp] * 14
     L.mpcb_step_host.restype = C.c_int
     L.mpcb_plant_step.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp]

@@ -949,3 +949,81 @@ int mpcb_measure_fp64_peak(int device, double* tflops_out) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// allocation-free step: mpcb_step with the longest-first launch order, its scratch in static device memory
+// ---------------------------------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops).  The step kernel's launch-order scratch (histogram + finished-warp
+// counter, per-problem ranks, slot -> problem table; see lpt_finish in mpcb_step.cuh) normally lives in the session slab
+// that mpcb_session_begin allocates.  Here it is a file-scope array that every GPU loading the library holds until exit:
+// words [0, 65) histogram + counter, word 128 the batch size of the last call, [256, 256 + MAX) order, then MAX ranks.
+namespace {
+constexpr int kStaticScratchHead = 256;
+constexpr size_t kStaticScratchWords = kStaticScratchHead + 2 * (size_t)MPCB_STATIC_MAX_BATCH;
+static __device__ __align__(256) int g_step_scratch[kStaticScratchWords];      // 129 KB per device
+
+// One CTA: the histogram and the counter must start at zero on every call; the slot -> problem table of the last call is
+// kept (that is the point: problems keep their cost from one control step to the next) unless the batch size changed,
+// in which case it is no permutation of this batch and is reset to the identity.
+__global__ void static_scratch_prepare(int* __restrict__ scr, int B) {
+    const bool fresh = scr[128] != B;
+    if (threadIdx.x < 65) scr[threadIdx.x] = 0;
+    if (fresh)
+        for (int i = threadIdx.x; i < B; i += blockDim.x) scr[kStaticScratchHead + i] = i;
+    __syncthreads();
+    if (threadIdx.x == 0) scr[128] = B;
+}
+
+constexpr int kMaxDevices = 64;
+int* g_step_scratch_ptr[kMaxDevices] = {};      // device address of g_step_scratch on each device (host code cannot use the name)
+
+// once per device, with that device current: the array's name is a host-side stand-in, only this gives the address
+int static_scratch_ptr(mpcb_handle* h, int** out) {
+    if (h->device < 0 || h->device >= kMaxDevices) { h->err = "mpcb_step_static: device index out of range"; return MPCB_EINVAL; }
+    if (!g_step_scratch_ptr[h->device]) {
+        int cur = -1;
+        CUDA_TRY(h, cudaGetDevice(&cur));
+        if (cur != h->device) CUDA_TRY(h, cudaSetDevice(h->device));
+        int* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_step_scratch);
+        if (cur != h->device) cudaSetDevice(cur);
+        if (e != cudaSuccess || !ptr) {
+            h->err = std::string("mpcb_step_static: cudaGetSymbolAddress(g_step_scratch): ") + cudaGetErrorString(e);
+            return MPCB_ECUDA;
+        }
+        g_step_scratch_ptr[h->device] = ptr;
+    }
+    *out = g_step_scratch_ptr[h->device];
+    return MPCB_OK;
+}
+}  // namespace
+
+extern "C" int mpcb_step_static(mpcb_handle* h, int B, const double* state_dev, const int* route_dev, const int* ncourse_dev,
+                                const double* L_dev, int* target_ind_dev, int* warm_dev, double* oa_dev, double* od_dev,
+                                double* traj_dev, double* xref_dev, double* di_ai_dev, double* xdev_dev, int* status_dev,
+                                int* iters_dev, void* stream) {
+    if (!h) return MPCB_EINVAL;
+    if (B <= 0 || !state_dev || !route_dev || !ncourse_dev || !target_ind_dev || !warm_dev ||
+        !oa_dev || !od_dev || !di_ai_dev || !status_dev) { h->err = "mpcb_step_static: bad arguments"; return MPCB_EINVAL; }
+    if (B > MPCB_STATIC_MAX_BATCH || B > h->max_batch) {
+        h->err = "mpcb_step_static: B=" + std::to_string(B) + " exceeds the static scratch (MPCB_STATIC_MAX_BATCH=" +
+                 std::to_string(MPCB_STATIC_MAX_BATCH) + ") or the handle's max_batch; use mpcb_step";
+        return MPCB_EINVAL;
+    }
+    if (h->cfg.T > 31) { h->err = "mpcb_step_static: the long-horizon kernel (T > 31) uses no scratch; use mpcb_step"; return MPCB_EINVAL; }
+    if (!h->courses_dev) { h->err = "mpcb_step_static: no courses set"; return MPCB_EINVAL; }
+    int* scr = nullptr;
+    int rc = static_scratch_ptr(h, &scr);
+    if (rc != MPCB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    static_scratch_prepare<<<1, 1024, 0, st>>>(scr, B);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches++;
+    StepParams p = make_params(h);
+    p.B = B; p.state = state_dev; p.route = route_dev; p.ncourse = ncourse_dev; p.L = L_dev;
+    p.target_ind = target_ind_dev; p.warm = warm_dev; p.oa = oa_dev; p.od = od_dev; p.traj = traj_dev;
+    p.xref = xref_dev; p.di_ai = di_ai_dev; p.xdev = xdev_dev; p.status = status_dev; p.iters = iters_dev;
+    p.lpt_hist = scr; p.lpt_order = scr + kStaticScratchHead; p.lpt_rank = scr + kStaticScratchHead + MPCB_STATIC_MAX_BATCH;
+    return dispatch_step(h, p, st);
+}
