@@ -66,7 +66,7 @@ typedef struct mpcb_config {
     double dt;             /* sample time (MPC.__init__ dt, default 0.2)                     */
     double wheelbase;      /* CarDimensions.distance_back_to_front_wheel used when L_dev==NULL (2.86) */
     /* interior-point controls (no reference counterpart: cvxpy->ECOS defaults are abstol=reltol=feastol=1e-8) */
-    int ipm_max_iter;      /* default 60                                                     */
+    int ipm_max_iter;      /* default 100                                                    */
     double ipm_tol_mu;     /* complementarity gap target, default 1e-12                      */
     double ipm_tol_p;      /* primal residual,             default 1e-10                     */
     double ipm_tol_d;      /* dual residual (absolute part), default 1e-9                    */

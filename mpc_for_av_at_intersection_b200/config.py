@@ -32,7 +32,7 @@ class MpcConfig:
     # not in the JSON: arguments of MPC.__init__ / car dimensions, and solver controls
     dt: float = 0.2
     wheelbase: float = 2.86
-    ipm_max_iter: int = 60
+    ipm_max_iter: int = 100
     ipm_tol_mu: float = 1e-12
     ipm_tol_p: float = 1e-10
     ipm_tol_d: float = 1e-9

@@ -199,10 +199,17 @@ int launch_step_long(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     return wide ? launch_step_long_nt<256>(h, p, st) : launch_step_long_nt<kLongThreads>(h, p, st);
 }
 
+#ifdef MPCB_TRACE
+double* g_trace_dev = nullptr;      // development builds only (scripts/trace_failures.py): per-iteration log [B][128][8]
+#endif
+
 StepParams make_params(const mpcb_handle* h) {
     const mpcb_config& c = h->cfg;
     StepParams p;
     memset(&p, 0, sizeof(p));
+#ifdef MPCB_TRACE
+    p.trace = g_trace_dev;
+#endif
     p.R = h->R; p.ncmax = h->ncmax; p.courses = h->courses_dev; p.dl = h->dl_dev;
     p.w_perp = c.w_perp; p.w_para = c.w_para; p.R0 = c.R[0]; p.R1 = c.R[1]; p.Rd0 = c.Rd[0]; p.Rd1 = c.Rd[1];
     p.Qv = c.Q_v_yaw[0]; p.Qyaw = c.Q_v_yaw[1];
@@ -233,7 +240,7 @@ void mpcb_default_config(mpcb_config* c) {
     c->max_steer = 45.0 * (3.141592653589793 / 180.0);      // np.deg2rad(45.0)
     c->max_speed = 30.0 / 3.6; c->min_speed = -5.0; c->r_end = 10.0; c->min_ref_speed = 10 / 3.6;
     c->dt = 0.2; c->wheelbase = 2.86;
-    c->ipm_max_iter = 60; c->ipm_tol_mu = 1e-12; c->ipm_tol_p = 1e-10; c->ipm_tol_d = 1e-9;
+    c->ipm_max_iter = 100; c->ipm_tol_mu = 1e-12; c->ipm_tol_p = 1e-10; c->ipm_tol_d = 1e-9;
     c->car_width = 2.0; c->car_length = 2.86 + 0.64;      // BicycleModelDimensions (car_dimensions.py:82-90)
     c->coupling_horizon = 7.0; c->frame_window = 20;      // mpc_intersection.py:81-82
 }
@@ -1027,3 +1034,7 @@ extern "C" int mpcb_step_static(mpcb_handle* h, int B, const double* state_dev, 
     p.lpt_hist = scr; p.lpt_order = scr + kStaticScratchHead; p.lpt_rank = scr + kStaticScratchHead + MPCB_STATIC_MAX_BATCH;
     return dispatch_step(h, p, st);
 }
+
+#ifdef MPCB_TRACE
+extern "C" void mpcb_debug_set_trace(double* trace_dev) { g_trace_dev = trace_dev; }
+#endif

@@ -394,27 +394,29 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
         const bool feasible0 = (hh8[6] >= -1e-9) && (hh8[7] >= -1e-9);
 
         double a = act ? oa : 0.0, d = act ? od : 0.0;
-        double s[8], lam[8];
-        {
-            double g[8];
-            G_apply(a, d, g);
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                s[c] = mk[c] ? fmax(hh8[c] - g[c], 1.0) : 1.0;
-                lam[c] = mk[c] ? 1.0 : 0.0;
-            }
-        }
         double gscale;
         {
             double g0a, g0d;
             gradient(0.0, 0.0, g0a, g0d);
             gscale = 1.0 + bo.max(fmax(fabs(g0a), fabs(g0d)));
         }
+        double s[8], lam[8];      // centred, gradient-scaled start: see mpcb_step.cuh
+        {
+            double g[8];
+            G_apply(a, d, g);
+            const double mu0 = fmax(10.0, 0.01 * gscale);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                s[c] = mk[c] ? fmax(hh8[c] - g[c], 1.0) : 1.0;
+                lam[c] = mk[c] ? mu0 * rcp(s[c]) : 0.0;
+            }
+        }
         double res_d = 1e300, res_p = 1e300, mu = 1e300;
         bool converged = false;
         int it = 0;
         double mu_prev = 1e300;
         bool eta_safe = false;
+        double best_m = 1e300, best_a = 0.0, best_d = 0.0;      // best iterate so far and its merit, see mpcb_step.cuh
         while (feasible0) {
             double rda, rdd, rp[8];
             {
@@ -433,6 +435,16 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                 mu = bo.sum(sl) / m_cnt;
                 res_d = bo.max(fmax(fabs(rda), fabs(rdd)));
                 res_p = bo.max(rpm);
+            }
+#ifdef MPCB_TRACE
+            if (p.trace && tid == 0 && it < 128) {
+                double* tr = p.trace + ((size_t)b * 128 + it) * 8;
+                tr[0] = it; tr[1] = res_d; tr[2] = res_p; tr[3] = mu; tr[5] = 1.0; tr[7] = gscale;
+            }
+#endif
+            {
+                const double m = fmax(fmax(res_d / (1e-8 * gscale), res_p * 1e9), mu * 1e9);
+                if (m < best_m && m < 100.0) { best_m = m; best_a = a; best_d = d; }
             }
             if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) { converged = true; break; }
             if (it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) break;
@@ -511,6 +523,9 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                 }
             }
             __syncthreads();
+#ifdef MPCB_TRACE
+            if (p.trace && tid == 0 && it < 128 && bad) p.trace[((size_t)b * 128 + it) * 8 + 6] = 1.0;
+#endif
             if (bad) break;
             // L D L' x = vec, in place
             auto solve = [&]() {
@@ -585,6 +600,9 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                 mu_prev = mu;
                 const double eta = eta_safe ? 0.99 : 1.0 - fmin(0.01, fmax(mu, 0.1 * p.tol_mu / mu));
                 const double al = (tmax > eta) ? eta / tmax : 1.0;
+#ifdef MPCB_TRACE
+                if (p.trace && tid == 0 && it < 128) p.trace[((size_t)b * 128 + it) * 8 + 4] = al;
+#endif
                 a += al * da; d += al * dd;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) { s[c] += al * dsa[c]; lam[c] += al * dla[c]; }
@@ -592,8 +610,8 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             ++it;
         }
         iters = it;
-        if (converged || (feasible0 && res_d < 1e-8 * gscale && res_p < 1e-9 && mu < 1e-9)) status = MPCB_ST_OPTIMAL;
-        else if (feasible0 && res_d < 1e-6 * gscale && res_p < 1e-7 && mu < 1e-7) status = MPCB_ST_INACCURATE;
+        if (converged) status = MPCB_ST_OPTIMAL;
+        else if (feasible0 && best_m < 100.0) { status = best_m < 1.0 ? MPCB_ST_OPTIMAL : MPCB_ST_INACCURATE; a = best_a; d = best_d; }
         else { status = MPCB_ST_FAILED; solved = false; break; }
         solved = true;
         oa = a; od = d;

@@ -201,8 +201,14 @@ class Condensed:
         h = self.h()
         a = np.zeros(T) if a0 is None else np.array(a0, float)
         d = np.zeros(T) if d0 is None else np.array(d0, float)
+        g0a, g0d = self.grad(np.zeros(T), np.zeros(T))
+        gscale = 1.0 + max(np.abs(g0a).max(), np.abs(g0d).max())
+        # the kernel's start: slacks floored at 1, multipliers centred on them with mu0 = max(10, gscale / 100)
         s = np.where(msk, np.maximum(h - self.G_apply(a, d), 1.0), 1.0)
-        lam = np.where(msk, 1.0, 0.0)
+        lam = np.where(msk, max(10.0, 0.01 * gscale) / s, 0.0)
+        if init == "legacy":                       # the round-1 start: lam = 1
+            lam = np.where(msk, 1.0, 0.0)
+            init = None
         if init is not None:                       # experiment hook: (slack floor, mu0) -> centred start lam = mu0 / s
             s = np.where(msk, np.maximum(h - self.G_apply(a, d), init[0]), 1.0)
             lam = np.where(msk, init[1] / s, 0.0)
@@ -212,8 +218,6 @@ class Condensed:
             lam = np.where(msk, np.maximum(lp, dl_), 0.0)
         m = msk.sum()
         status = 1
-        g0a, g0d = self.grad(np.zeros(T), np.zeros(T))
-        gscale = 1.0 + max(np.abs(g0a).max(), np.abs(g0d).max())
         mu_prev, eta_safe = 1e300, False
         for it in range(1, max_iter + 1):
             ga, gd = self.grad(a, d)

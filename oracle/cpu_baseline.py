@@ -73,37 +73,44 @@ def run(courses, workload, ids, steps, T, L, dt, cores=None):
     return dict(solves=solves, seconds=wall, cores=cores, per_core_busy_s=[r[1] for r in res], controls=controls)
 
 
-def run_cpp(courses_smoothed, workload, n, steps, cfg, cores=None, min_seconds=0.0, max_steps=2000, reset_every=40):
+def run_cpp(courses_smoothed, workload, n, steps, cfg, cores=None, min_seconds=0.0, max_steps=2000, lead_in=5, phase_len=20):
     """Same closed loops through the plain C++ port (oracle/mpc_port.cpp), `cores` std::threads inside one call per
-    control step; the plant step between calls is the vectorised host twin of Simulation.step.
-    `courses_smoothed`: CourseSet with smooth=True (the port, like MPC.__init__, works on smoothed yaws).
-    Runs at least `steps` control steps and keeps going until `min_seconds` of wall time have passed.
-    Returns dict(solves, seconds (wall), cores, failed, steps)."""
+    control step; the plant step between calls is the vectorised host twin of Simulation.step (not timed: in the
+    reference the scenario script owns the simulation).  Same step mix as the GPU arm of bench.py: every cycle starts
+    the closed loops from the workload's cold start, runs `lead_in` untimed control steps and then times up to
+    `phase_len` steps (control steps lead_in .. lead_in + phase_len - 1).  Only `step_batch` is inside the clock.
+    `courses_smoothed`: CourseSet with smoothed yaws (the port, like MPC.__init__, works on smoothed yaws).
+    Runs at least `steps` timed control steps and keeps going until `min_seconds` of timed work have passed.
+    Returns dict(solves, seconds (timed), cores, failed, steps, wall)."""
     import mpc_port
     from mpc_for_av_at_intersection_b200.scenarios import host_plant_step
     cores = int(cores or os.cpu_count() or 1)
     T = int(cfg.T)
     cfgvec = mpc_port.pack_config(cfg)
     mpc_port.lib()
-    state = np.ascontiguousarray(workload["state"][:n]).copy()
     route = np.ascontiguousarray(workload["route"][:n]).astype(np.int32)
     ncourse = courses_smoothed.length[route].astype(np.int32)
-    target = np.ascontiguousarray(workload["target_ind"][:n]).astype(np.int32)
-    warm = np.zeros(n, np.int32)
-    oa = np.zeros((n, T)); od = np.zeros((n, T)); di_ai = np.zeros((n, 2))
     L = np.full(n, float(cfg.wheelbase))
     solves = failed = 0
-    t0 = time.perf_counter()
+    timed = 0.0
+    t_wall = time.perf_counter()
     k = 0
-    while k < steps or (time.perf_counter() - t0 < min_seconds and k < max_steps):
-        if k and reset_every and k % reset_every == 0:          # start the same closed loops again (same mix of steps)
-            state = np.ascontiguousarray(workload["state"][:n]).copy()
-            target = np.ascontiguousarray(workload["target_ind"][:n]).astype(np.int32)
-            warm[:] = 0
-        k += 1
-        out = mpc_port.step_batch(cfgvec, courses_smoothed.packed, courses_smoothed.dl, state, route, ncourse, L, target, warm,
-                                  oa, od, di_ai, want_traj=False, nthreads=cores)
-        solves += n
-        failed += int((out["status"] >= 2).sum())
-        state = host_plant_step(state, di_ai[:, 0], di_ai[:, 1], float(cfg.wheelbase), float(cfg.dt))
-    return dict(solves=solves, seconds=time.perf_counter() - t0, cores=cores, failed=failed, steps=k)
+    while k < steps or (timed < min_seconds and k < max_steps):
+        state = np.ascontiguousarray(workload["state"][:n]).copy()           # the same cold start every cycle
+        target = np.ascontiguousarray(workload["target_ind"][:n]).astype(np.int32)
+        warm = np.zeros(n, np.int32)
+        oa = np.zeros((n, T)); od = np.zeros((n, T)); di_ai = np.zeros((n, 2))
+        for j in range(lead_in + phase_len):
+            is_timed = j >= lead_in
+            if is_timed and not (k < steps or (timed < min_seconds and k < max_steps)):
+                break
+            t0 = time.perf_counter()
+            out = mpc_port.step_batch(cfgvec, courses_smoothed.packed, courses_smoothed.dl, state, route, ncourse, L, target, warm,
+                                      oa, od, di_ai, want_traj=False, nthreads=cores)
+            if is_timed:
+                timed += time.perf_counter() - t0
+                k += 1
+                solves += n
+                failed += int((out["status"] >= 2).sum())
+            state = host_plant_step(state, di_ai[:, 0], di_ai[:, 1], float(cfg.wheelbase), float(cfg.dt))
+    return dict(solves=solves, seconds=timed, cores=cores, failed=failed, steps=k, wall=time.perf_counter() - t_wall)

@@ -2,6 +2,7 @@
 
 Only tests/, __graft_entry__.smoke()/build() and bench.py's CPU legs may import this module."""
 import ctypes as C
+import hashlib
 import os
 import subprocess
 
@@ -9,18 +10,39 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "mpc_port.cpp")
-LIB = os.path.join(HERE, "_build", "libmpcport.so")
 _lib = None
 
 
+def cpu_model():
+    """(model name, flags hash) of the host CPU: the port is built -march=native, so a library built on another CPU
+    model must not be reused (the build container and the GPU box differ)."""
+    name, flags = "unknown", ""
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name") and name == "unknown":
+                name = ln.split(":", 1)[1].strip()
+            elif ln.startswith("flags") and not flags:
+                flags = ln.split(":", 1)[1].strip()
+            if name != "unknown" and flags:
+                break
+    except OSError:
+        pass
+    return name, hashlib.sha1((name + flags).encode()).hexdigest()[:10]
+
+
+LIB = os.path.join(HERE, "_build", f"libmpcport.{cpu_model()[1]}.so")
+
+
 def build(force=False):
-    """g++ -O2 -shared (no external libraries); returns the path of the library."""
+    """g++ -O3 -march=native -shared (no external libraries), one library per host CPU model; returns its path."""
     if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(SRC):
         os.makedirs(os.path.dirname(LIB), exist_ok=True)
-        cmd = ["g++", "-O2", "-shared", "-fPIC", "-std=c++17", "-pthread", SRC, "-o", LIB]
+        tmp = LIB + f".{os.getpid()}.tmp"
+        cmd = ["g++", "-O3", "-march=native", "-shared", "-fPIC", "-std=c++17", "-pthread", SRC, "-o", tmp]
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError("g++ failed:\n" + res.stderr[-3000:])
+        os.replace(tmp, LIB)
     return LIB
 
 

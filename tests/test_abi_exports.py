@@ -61,6 +61,8 @@ def test_smooth_yaw_matches_oracle(lib):
         lib.mpcb_smooth_yaw(a.ctypes.data_as(C.c_void_p), len(a))
         mo.smooth_yaw(b)
         assert np.array_equal(a, b)
+        from mpc_for_av_at_intersection_b200.courses import smooth_yaw_host
+        assert np.array_equal(smooth_yaw_host(yaw.copy()), a)       # the library-free twin used by bench.py's CPU arm
 
 
 def test_no_cpu_fallback(lib):
