@@ -2,6 +2,7 @@
 """bench.py -- MPC solves/sec of the batched B200 MPC tracking loop (BASELINE.json metric).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--batch B] [--horizon T]
+                    [--workload config2|sweep]
 
 Workload (config.workload): BASELINE.json configs[1] -- 4,096 independent ego vehicles per GPU on randomised
 intersection scenarios, horizon N=20, closed loop (every step: MPC.step for the whole batch, then the plant
@@ -9,15 +10,24 @@ step).  One "step" = one control step of the whole batch = B solves.  N>1: one p
 scenarios sharded by rank, no data-path collective ("scaling": "weak"); the only collective is the timing
 reduction (max over ranks).
 
+The timed steps are ALWAYS control steps 5..24 of the closed loops that start at the workload's cold start
+(PHASE_LEAD untimed lead-in steps, then up to PHASE_LEN timed ones; for --steps > 20 the same start is re-seeded and
+the lead-in repeated, untimed).  The interior-point iterations per solve depend on how far a loop has settled, so a
+number that followed --steps/--warmup could not be compared between rounds; this one does not.  `mean_ipm_iters` and
+`ipm_iterations_per_sec` (= value x mean_ipm_iters) are printed so that two kernels can be compared even if the
+iteration count moves.
+
   value     solves/s with states resident in HBM (one fused kernel launch per control step, CUDA-event timed
             per step on the launching stream, L2 flushed between timed steps)
   e2e       solves/s through the host-buffer C-ABI call mpcb_session_step_host (MpcSession.step): vehicle
             states copied host->device and applied controls + status device->host inside the timed region
   roofline  FP64-FMA roofline of the step kernel: algorithmic flops F(T, Nc, K) of SURVEY.md section 8d x
             solves per launch / average launch duration, against the FP64 FMA peak measured live
-  cpu_baseline  the oracle port (numpy float64, oracle/mpc_oracle.py) on the host cores, bounded sample
+  cpu_baseline  the plain C++ port of main/lib/mpc.py (oracle/mpc_port.cpp, -O3 -march=native, all host threads) on a
+            bounded sample of the same workload and the same control steps; only the solver call is inside its clock
 
-`--impl reference` times that CPU port alone, on all host cores, and prints the same line shape."""
+`--impl reference` times that CPU port alone, on all host cores, and prints the same line shape.
+`--workload sweep` runs BASELINE.json configs[3] (1,048,576-scenario closed-loop sweep, strong scaling, NCCL gather)."""
 import argparse
 import json
 import os
@@ -31,6 +41,7 @@ sys.path.insert(0, REPO)
 
 METRIC = "mpc_solves_per_sec"
 UNIT = "solves/s"
+PHASE_LEAD, PHASE_LEN = 5, 20      # timed steps = control steps 5..24 of the closed loops, whatever --steps/--warmup
 
 
 def algorithmic_flops(T, nc_scanned, K):
@@ -99,55 +110,66 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def cpu_arm(args, courses, cfg, per_core_problems, steps_each, cores=None):
-    """Time the CPU port (oracle/mpc_port.cpp, all host cores) on a bounded sample of the bench workload.
-    Returns (dict, solves/s)."""
+def workload_string(B, T):
+    """config.workload, identical in both arms (the driver compares the strings)."""
+    return (f"BASELINE.json configs[1]: {B} independent ego vehicles per GPU on randomised intersection scenarios "
+            f"(12 A* routes), horizon N={T}, closed loop (MPC.step + plant step per control step), timed steps = "
+            f"control steps {PHASE_LEAD}..{PHASE_LEAD + PHASE_LEN - 1} from the cold start")
+
+
+def host_cpu():
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    import mpc_port
+    return mpc_port.cpu_model()[0]
+
+
+def probe_cvxpy_ecos():
+    """BASELINE.md section 3.1 / SURVEY.md section 8c: is the reference's real solver stack on this box?"""
+    try:
+        import cvxpy  # noqa: F401
+        import ecos  # noqa: F401
+        return os.path.basename(os.path.dirname(getattr(cvxpy, "__file__", "") or "")) != "cvxpy_shim" and hasattr(cvxpy, "ECOS")
+    except Exception:
+        return False
+
+
+def cpu_sample(args, courses, cfg, n, steps, min_seconds, cores=None):
+    """Time the CPU port (oracle/mpc_port.cpp, all host cores) on the first `n` problems of the bench workload, same
+    control steps as the GPU arm.  Returns (cpu_baseline dict, run dict)."""
     sys.path.insert(0, os.path.join(REPO, "oracle"))
     import cpu_baseline
     from mpc_for_av_at_intersection_b200.scenarios import make_workload
     cores = cores or os.cpu_count() or 1
-    n = min(args.batch, 4096)
     wl = make_workload(courses, n, seed=args.seed, first=0)
-    cpu_baseline.run_cpp(courses, wl, min(n, 64), 1, cfg, cores=cores)          # load / page in
-    r = cpu_baseline.run_cpp(courses, wl, n, steps_each, cfg, cores=cores, min_seconds=args.cpu_seconds)
+    cpu_baseline.run_cpp(courses, wl, min(n, 64), 1, cfg, cores=cores, lead_in=0)          # load / page in
+    r = cpu_baseline.run_cpp(courses, wl, n, steps, cfg, cores=cores, min_seconds=min_seconds, lead_in=PHASE_LEAD, phase_len=PHASE_LEN)
     v = r["solves"] / r["seconds"]
-    return ({"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port",
-             "sample": f"first {n} problems of the workload x {r['steps']} closed-loop steps = {r['solves']} solves "
-                       f"in {r['seconds']:.1f} s wall on {r['cores']} threads; plain C++ float64 port oracle/mpc_port.cpp "
-                       f"(generic dense condensing + dense Mehrotra IPM in place of cvxpy+ECOS, which like "
-                       f"/root/reference is not on this box)"}, v)
+    return ({"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port", "cpu_model": host_cpu(),
+             "sample": f"first {n} problems of the workload x {r['steps']} timed control steps (steps {PHASE_LEAD}..{PHASE_LEAD + PHASE_LEN - 1} "
+                       f"of the closed loops, re-seeded) = {r['solves']} solves in {r['seconds']:.1f} s of solver time on {r['cores']} threads "
+                       f"({r['failed']} failed); plain C++ float64 port oracle/mpc_port.cpp (-O3 -march=native; generic dense condensing + "
+                       f"dense Mehrotra IPM in place of cvxpy+ECOS, which like /root/reference is not on this box)"}, r)
 
 
 def run_reference(args):
     """--impl reference: the CPU port on all host cores; a step = one control step of a bounded sample (<= 4096
-    problems) of the same workload."""
+    problems) of the same workload, same control steps as the GPU arm.  This process never maps libmpcb.so."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     from mpc_for_av_at_intersection_b200 import CourseSet, MpcConfig, load_intersection_routes
-    sys.path.insert(0, os.path.join(REPO, "oracle"))
-    import cpu_baseline
-    from mpc_for_av_at_intersection_b200.scenarios import make_workload
     cfg = MpcConfig.from_json(T=args.horizon)
-    courses = CourseSet(load_intersection_routes())
-    cores = os.cpu_count() or 1
+    courses = CourseSet(load_intersection_routes(), smooth="numpy")
     per_step = min(args.batch, 4096) if cfg.T <= 20 else min(args.batch, 256)
-    wl = make_workload(courses, per_step, seed=args.seed, first=0)
-    if args.warmup > 0:
-        cpu_baseline.run_cpp(courses, wl, per_step, min(args.warmup, 3), cfg, cores=cores)
-    r = cpu_baseline.run_cpp(courses, wl, per_step, args.steps, cfg, cores=cores)
-    v = r["solves"] / r["seconds"]
-    sample = (f"{per_step} problems x {args.steps} closed-loop steps = {r['solves']} solves in {r['seconds']:.1f} s wall on "
-              f"{r['cores']} threads; plain C++ float64 port of main/lib/mpc.py (oracle/mpc_port.cpp: generic dense condensing + "
-              f"dense Mehrotra IPM; the reference's cvxpy+ECOS stack is not installable offline), {r['failed']} failed solves")
+    cpu, r = cpu_sample(args, courses, cfg, per_step, args.steps, 0.0)
+    v = cpu["value"]
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * r["seconds"] / max(args.steps, 1), "higher_is_better": True,
+        "warmup": args.warmup, "ms_per_step": 1e3 * r["seconds"] / max(r["steps"], 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"BASELINE.json configs[1]: independent ego vehicles on randomised intersection "
-                               f"scenarios, horizon N={cfg.T}, closed loop; bounded sample of {per_step} problems "
-                               f"per step", "horizon": cfg.T, "problems_per_step": per_step, "seed": args.seed},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample},
+        "config": {"workload": workload_string(args.batch, cfg.T), "batch_per_gpu": args.batch, "horizon": cfg.T, "seed": args.seed,
+                   "sample": f"bounded sample: the first {per_step} problems of the workload per step", "failed_solves": r["failed"]},
+        "cpu_baseline": cpu, "cvxpy_ecos_present": probe_cvxpy_ecos(),
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -184,7 +206,8 @@ def run_b200(args):
     # ---- CPU baseline first (fork pool before CUDA is initialised), rank 0 at N=1 only ---------------------
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        cpu, _ = cpu_arm(args, courses, cfg, args.cpu_problems_per_core, args.cpu_steps)
+        cpu, _ = cpu_sample(args, courses, cfg, min(args.batch, 4096) if cfg.T <= 20 else min(args.batch, 256), args.cpu_steps,
+                            args.cpu_seconds)
 
     import numpy as np
     import torch
@@ -198,8 +221,7 @@ def run_b200(args):
     lib = _lib.lib()
 
     wl = make_workload(courses, B, seed=args.seed, first=rank * B)     # shard = contiguous scenario range
-    ses = MpcSession(cfg, courses, B, device=local).begin(wl["route"], target_ind=wl["target_ind"])
-    ses.store("state", wl["state"])
+    ses = MpcSession(cfg, courses, B, device=local)
     stream = torch.cuda.Stream(device=dev)
     sptr = stream.cuda_stream
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
@@ -210,10 +232,18 @@ def run_b200(args):
             dist.barrier()
             torch.cuda.synchronize(dev)
 
+    def reseed_dev(lead):
+        """the workload's cold start, then `lead` untimed control steps on the device"""
+        ses.begin(wl["route"], target_ind=wl["target_ind"])
+        ses.store("state", wl["state"])
+        with torch.cuda.stream(stream):
+            for _ in range(lead):
+                ses.closed_loop_dev(1, 0, sptr, goal_test=False)
+        torch.cuda.synchronize(dev)
+
     # ---- device-resident closed loop: value -----------------------------------------------------------------
-    with torch.cuda.stream(stream):
-        for _ in range(args.warmup):
-            ses.closed_loop_dev(1, 0, sptr, goal_test=False)
+    reseed_dev(args.warmup)                                 # W untimed warm-up steps (clocks, caches, function attributes)
+    reseed_dev(PHASE_LEAD)
     barrier()
     sampler = ClockSampler(local).start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
@@ -225,9 +255,13 @@ def run_b200(args):
     status_v = torch.as_tensor(ses.device_view("status"), device=dev)
     bad_acc = torch.zeros((), dtype=torch.int64, device=dev)
     l0 = ses.launches
+    lead_launches = 0
     t_wall0 = time.perf_counter()
-    with torch.cuda.stream(stream):
-        for k in range(args.steps):
+    for k in range(args.steps):
+        if k and k % PHASE_LEN == 0:                        # same loops again: the timed steps stay control steps 5..24
+            reseed_dev(PHASE_LEAD)
+            lead_launches += PHASE_LEAD
+        with torch.cuda.stream(stream):
             flush.zero_()                                   # L2 flush, outside the event pair
             scan_acc += (nc_v - tgt_v).clamp_(min=0)        # course points scanned by this step's lookup
             ev[k][0].record(stream)
@@ -237,7 +271,7 @@ def run_b200(args):
             bad_acc += (status_v >= 2).sum()
     barrier()
     t_wall1 = time.perf_counter()
-    launches = ses.launches - l0
+    launches = ses.launches - l0 - lead_launches
     step_ms = [a.elapsed_time(b) for a, b in ev]
     dev_ms = float(sum(step_ms))
     clocks = sampler.stop(t_wall0, t_wall1)
@@ -249,16 +283,23 @@ def run_b200(args):
     scan_mean = float(scan_acc.double().mean().item()) / max(args.steps, 1)
     n_bad = int(bad_acc.item())
 
-    # ---- end to end through the host-buffer C ABI -----------------------------------------------------------------
-    ses.begin(wl["route"], target_ind=wl["target_ind"])
-    state = np.ascontiguousarray(wl["state"])
+    # ---- end to end through the host-buffer C ABI, same control steps ------------------------------------------------
     L = cfg.wheelbase
-    for _ in range(args.warmup):
-        d, a = ses.step(state)
-        state = host_plant_step(state, d, a, L, cfg.dt)
+
+    def reseed_host(lead):
+        ses.begin(wl["route"], target_ind=wl["target_ind"])
+        st = np.ascontiguousarray(wl["state"])
+        for _ in range(lead):
+            d, a = ses.step(st)
+            st = host_plant_step(st, d, a, L, cfg.dt)
+        return st
+
+    state = reseed_host(PHASE_LEAD)
     barrier()
     e2e_s = 0.0
-    for _ in range(args.steps):
+    for k in range(args.steps):
+        if k and k % PHASE_LEN == 0:
+            state = reseed_host(PHASE_LEAD)
         t0 = time.perf_counter()
         d, a = ses.step(state)                               # H2D state, kernel, D2H controls + status, sync
         e2e_s += time.perf_counter() - t0
@@ -283,13 +324,12 @@ def run_b200(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms_max / args.steps, "p50_step_ms": sorted(step_ms)[len(step_ms) // 2],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"BASELINE.json configs[1]: {B} independent ego vehicles per GPU on randomised "
-                                   f"intersection scenarios (12 A* routes), horizon N={T}, closed loop "
-                                   f"(MPC.step + plant step per control step)",
+            "config": {"workload": workload_string(B, T),
                        "batch_per_gpu": B, "horizon": T, "seed": args.seed, "sharding": f"scenarios x{world}",
                        "l2": "flushed between timed steps (256 MiB memset outside the event pairs)",
-                       "mean_ipm_iters": k_mean, "mean_course_points_scanned": scan_mean,
-                       "failed_solves": n_bad},
+                       "mean_ipm_iters": k_mean, "ipm_iterations_per_sec": value * k_mean,
+                       "mean_course_points_scanned": scan_mean, "failed_solves": n_bad},
+            "cvxpy_ecos_present": probe_cvxpy_ecos(),
             "clocks": clocks,
             "e2e": {"value": B * world * args.steps / e2e_s_max, "unit": UNIT,
                     "h2d_bytes_per_step": 32 * B, "d2h_bytes_per_step": 20 * B,
@@ -314,6 +354,104 @@ def run_b200(args):
     return 0
 
 
+def run_sweep(args):
+    """--workload sweep: BASELINE.json configs[3] -- `--scenarios` single-ego closed loops (the config-2 generator), STRONG
+    scaling: rank r owns shard_range(n, r, N), chunks of `--chunk` resident scenarios, `--sweep-steps` control steps with
+    the goal test on, float32 history [scenarios/N, steps, 8] and per-scenario statistics kept on the device, then ONE
+    NCCL all-gather device -> device per array and one D2H of the union on rank 0.  The workload is generated on the host
+    before the clock starts (reported as gen_s)."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    import torch
+    from mpc_for_av_at_intersection_b200 import CourseSet, MpcConfig, _lib, load_intersection_routes
+    from mpc_for_av_at_intersection_b200.sweep import checksum, gather_results, run_closed_loop_sweep
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    cfg = MpcConfig.from_json(T=args.horizon)
+    courses = CourseSet(load_intersection_routes())
+    n, K = args.scenarios, args.sweep_steps
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    # warm-up: a small sweep (function attributes, clocks, NCCL communicator)
+    w, _ = run_closed_loop_sweep(cfg, courses, 4096 * world, max(args.warmup, 3), seed=args.seed, chunk=args.chunk, rank=rank,
+                                 world=world, device=local)
+    gather_results({"steps_run": w["steps_run"]}, 4096 * world)
+    del w
+    barrier()
+    host = None
+    if rank == 0:                                               # pinned landing buffers of the union, allocated before the clock
+        shapes = dict(history=((n, K, 8), torch.float32), steps_run=((n,), torch.int32), reached_goal=((n,), torch.int32),
+                      final_state=((n, 4), torch.float64), fail_count=((n,), torch.int32), ipm_iters=((n,), torch.int64))
+        host = {k: torch.empty(sh, dtype=dt, pin_memory=True) for k, (sh, dt) in shapes.items()}
+    sampler = ClockSampler(local).start()
+    t0 = time.perf_counter()
+    res, tm = run_closed_loop_sweep(cfg, courses, n, K, seed=args.seed, chunk=args.chunk, rank=rank, world=world, device=local)
+    barrier()
+    t_loop = time.perf_counter()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record()
+    full = gather_results(res, n)
+    g1.record()
+    barrier()
+    gather_ms = g0.elapsed_time(g1)
+    t_gather = time.perf_counter()
+    gathered_bytes = sum(v.numel() * v.element_size() for v in full.values())
+    if rank == 0:                                               # one D2H of the union
+        for k, v in full.items():
+            host[k].copy_(v, non_blocking=True)
+        torch.cuda.synchronize(dev)
+    t_end = time.perf_counter()
+    clocks = sampler.stop(t0, t_end)
+    stats = torch.tensor([tm["loop_ms"], tm["gen_s"], gather_ms], dtype=torch.float64, device=dev)
+    solves = torch.tensor([tm["solves"]], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+        dist.all_reduce(solves, op=dist.ReduceOp.SUM)
+    loop_ms, gen_s, gather_ms = (float(x) for x in stats.tolist())
+    if rank == 0:
+        total = int(solves.item())
+        csum = checksum(full)
+        k_mean = float(full["ipm_iters"].sum().item()) / max(total, 1)
+        line = {
+            "metric": METRIC, "value": total / (loop_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
+            "ms_per_step": loop_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": f"BASELINE.json configs[3]: {n}-scenario closed-loop sweep (config-2 generator, seed {args.seed}), "
+                                   f"horizon N={cfg.T}, {K} control steps with the goal test on, sharded by scenario over {world} GPU(s) "
+                                   f"in chunks of {args.chunk}, NCCL all-gather of history + statistics at the end",
+                       "scenarios": n, "horizon": cfg.T, "seed": args.seed, "chunk": args.chunk, "mean_ipm_iters": k_mean,
+                       "l2": "inputs larger than L2 (65536 resident problems x 25.6 KB of per-problem state)"},
+            "clocks": clocks,
+            "sweep": {"solves": total, "reached_goal": int(full["reached_goal"].sum().item()), "failed_solves": int(full["fail_count"].sum().item()),
+                      "workload_gen_s_untimed": gen_s, "closed_loops_ms_device_max_over_ranks": loop_ms,
+                      "wall_s_loops": t_loop - t0, "wall_s_gather": t_gather - t_loop, "wall_s_d2h_rank0": t_end - t_gather,
+                      "wall_s_total": t_end - t0, "gather_ms": gather_ms, "gathered_bytes": gathered_bytes,
+                      "gather_gbs_per_gpu_received": gathered_bytes * (world - 1) / world / (gather_ms * 1e-3) / 1e9 if world > 1 else None,
+                      "d2h_bytes": gathered_bytes, "checksum": f"{csum:016x}",
+                      "history": f"float32 [{n}, {K}, 8] on the device, union on every rank after the gather"},
+            "e2e": {"value": total / (t_end - t0), "unit": UNIT, "h2d_bytes_per_step": 44 * n // K // world, "d2h_bytes_per_step": gathered_bytes // K,
+                    "api": "sweep.run_closed_loop_sweep + gather_results: host workload in, gathered union on the host out (wall clock incl. "
+                           "workload upload, closed loops, NCCL gather, D2H)"},
+            "gpu_launches": K * ((n // world + args.chunk - 1) // args.chunk),
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
 def C_double_peak(lib, device):
     import ctypes as C
     v = C.c_double(0.0)
@@ -331,14 +469,18 @@ def main():
     ap.add_argument("--horizon", type=int, default=20)
     ap.add_argument("--seed", type=int, default=1235)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-problems-per-core", type=int, default=4)
     ap.add_argument("--cpu-steps", type=int, default=12, help="closed-loop steps of the cpu_baseline sample (<= 4096 problems)")
-    ap.add_argument("--ref-problems-per-core", type=int, default=2)
-    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="minimum wall time of the cpu_baseline sample")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="minimum solver time of the cpu_baseline sample")
+    ap.add_argument("--workload", default="config2", choices=["config2", "sweep"], help="sweep = BASELINE.json configs[3]")
+    ap.add_argument("--scenarios", type=int, default=1 << 20, help="sweep: scenarios over ALL ranks (strong scaling)")
+    ap.add_argument("--sweep-steps", type=int, default=80, help="sweep: closed-loop control steps per scenario")
+    ap.add_argument("--chunk", type=int, default=65536, help="sweep: scenarios resident per launch")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
-    return run_reference(args) if args.impl == "reference" else run_b200(args)
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_sweep(args) if args.workload == "sweep" else run_b200(args)
 
 
 if __name__ == "__main__":

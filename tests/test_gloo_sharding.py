@@ -30,6 +30,9 @@ def _worker(rank, world, port, n_total, q):
         local = dict(final_state=wl["state"] * 2.0, steps_to_goal=(wl["route"] * 3 + 1).astype(np.int32),
                      ids=np.arange(first, first + count, dtype=np.int64))
         full = gather_results(local, n_total)
+        import torch
+        tens = gather_results({"ids": torch.from_numpy(local["ids"])}, n_total)      # tensors in -> tensors out (the GPU path)
+        assert torch.is_tensor(tens["ids"]) and torch.equal(tens["ids"], torch.arange(n_total))
         ref = make_workload(cs, n_total, seed=9)
         ok = (np.array_equal(full["ids"], np.arange(n_total)) and
               np.array_equal(full["final_state"], ref["state"] * 2.0) and

@@ -120,19 +120,71 @@ def test_sharded_sweep_is_union_of_single(T=20):
 
 
 def test_closed_loop_sweep_chunks_and_shards():
-    """run_closed_loop_sweep: chunked processing and a 2-way shard give the same per-scenario results as one pass."""
+    """run_closed_loop_sweep: chunked processing and a 2-way shard give the same per-scenario results as one pass, bit for
+    bit (results stay on the device; the checksum is the one bench.py --workload sweep prints)."""
+    import torch
     from mpc_for_av_at_intersection_b200 import CourseSet, MpcConfig
-    from mpc_for_av_at_intersection_b200.sweep import run_closed_loop_sweep
+    from mpc_for_av_at_intersection_b200.sweep import checksum, run_closed_loop_sweep
     cfg = MpcConfig.from_json(T=20)
     cs = CourseSet(load_routes(False))
-    one = run_closed_loop_sweep(cfg, cs, 300, 12, seed=3, chunk=4096, keep_history=True)
-    chunked = run_closed_loop_sweep(cfg, cs, 300, 12, seed=3, chunk=128)
-    halves = [run_closed_loop_sweep(cfg, cs, 300, 12, seed=3, rank=r, world=2) for r in range(2)]
-    for k in ("steps_to_goal", "final_state", "fail_count"):
-        assert np.array_equal(one[k], chunked[k]), k
-        assert np.array_equal(one[k], np.concatenate([h[k] for h in halves])), k
-    assert one["history"].shape == (300, 12, 8) and (one["fail_count"] == 0).all()
-    assert np.isfinite(one["final_state"]).all()
+    one, t1 = run_closed_loop_sweep(cfg, cs, 300, 12, seed=3, chunk=4096)
+    chunked, _ = run_closed_loop_sweep(cfg, cs, 300, 12, seed=3, chunk=128)
+    halves = [run_closed_loop_sweep(cfg, cs, 300, 12, seed=3, rank=r, world=2)[0] for r in range(2)]
+    union = {k: torch.cat([h[k] for h in halves], dim=0) for k in one}
+    for k in one:
+        assert one[k].is_cuda
+        assert torch.equal(one[k].view(torch.uint8), chunked[k].view(torch.uint8)), k
+        assert torch.equal(one[k].view(torch.uint8), union[k].view(torch.uint8)), k
+    assert checksum(one) == checksum(union) == checksum(chunked)
+    assert one["history"].shape == (300, 12, 8) and one["history"].dtype == torch.float32
+    assert int(one["fail_count"].sum()) == 0 and torch.isfinite(one["final_state"]).all()
+    assert t1["solves"] == int(one["steps_run"].sum()) == 300 * 12      # nobody reaches the goal in 12 steps
+    assert int(one["ipm_iters"].min()) >= 12 * 3
+
+
+def _nccl_gather_worker(rank, world, port, n_total, nsteps, q):
+    import os
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from mpc_for_av_at_intersection_b200 import CourseSet, MpcConfig, load_intersection_routes
+        from mpc_for_av_at_intersection_b200.sweep import checksum, gather_results, run_closed_loop_sweep
+        cfg = MpcConfig.from_json(T=20)
+        cs = CourseSet(load_intersection_routes())
+        local, _ = run_closed_loop_sweep(cfg, cs, n_total, nsteps, seed=5, chunk=512, rank=rank, world=world, device=rank)
+        full = gather_results(local, n_total)
+        assert all(v.is_cuda and v.shape[0] == n_total for v in full.values())      # device -> device, no host bounce
+        q.put((rank, checksum(full)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_nccl_gather_of_a_sharded_sweep_equals_the_single_gpu_sweep():
+    """BASELINE.json configs[3] in small: two ranks, two GPUs, ragged shards (1001 scenarios), NCCL all-gather of the
+    device-resident results; the union must be the 1-GPU sweep bit for bit.  Skipped on a one-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import socket
+    import torch.multiprocessing as mp
+    from mpc_for_av_at_intersection_b200 import CourseSet, MpcConfig
+    from mpc_for_av_at_intersection_b200.sweep import checksum, run_closed_loop_sweep
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    n_total, nsteps = 1001, 10
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_nccl_gather_worker, args=(r, 2, port, n_total, nsteps, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=300) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    one, _ = run_closed_loop_sweep(MpcConfig.from_json(T=20), CourseSet(load_routes(False)), n_total, nsteps, seed=5, chunk=512)
+    assert got[0] == got[1] == checksum(one)
 
 
 def test_longest_first_launch_order_changes_nothing():
