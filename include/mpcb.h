@@ -38,7 +38,11 @@ extern "C" {
 
 /* per-problem status written to status[B] */
 #define MPCB_ST_OPTIMAL 0     /* cvxpy.OPTIMAL            (main/lib/mpc.py:196)  */
-#define MPCB_ST_INACCURATE 1  /* cvxpy.OPTIMAL_INACCURATE (accepted, ibid.)      */
+#define MPCB_ST_INACCURATE 1  /* THIS solver's reduced residual class (dual 1e-6 x gradient scale, primal 1e-7, gap 1e-7 on
+                                 a verified iterate), accepted like cvxpy.OPTIMAL_INACCURATE is (ibid.).  It is an analogue, not
+                                 ECOS's own class: cvxpy -> ECOS is absent from the reference tree and unpinned, so which
+                                 problems ECOS would call inaccurate cannot be reproduced.  OPTIMAL (0) means the configured
+                                 tolerances or at least the 1e-8 class on a verified iterate.                          */
 #define MPCB_ST_FAILED 2      /* solve failed: ai = MAX_DECEL, di kept, warm start dropped (mpc.py:204-208,294-297) */
 #define MPCB_ST_NEAREST 3     /* Exception("something wrong") in calc_nearest_index_in_direction
                                  (main/lib/trajectories.py:120): the problem's state is left untouched */
@@ -231,7 +235,8 @@ int mpcb_session_store_host(mpcb_handle* h, int what, const void* src, long long
  *   obs_dev       [B,MPCB_MAX_OBSTACLES,6] obstacle states in MovingObstacle*.get() order (x, y, v, yaw, a, steer);
  *                 ignored (may be NULL) when vehicles_per_scenario > 0
  *   n_obs_dev     [B]    obstacles per ego (<= MPCB_MAX_OBSTACLES), NULL = 0
- *   done_dev      [B] or NULL: finished egos are skipped (their cut is kept)
+ *   done_dev      [B] or NULL: finished egos are skipped (their cut is kept); in/out: an ego whose nearest-index lookup
+ *                 hits the reference's Exception("something wrong") (main/lib/trajectories.py:120) is marked 2 (dead)
  *   agent_idx_dev [B]    in/out  traj_agent_idx
  *   ncourse_dev   [B]    in/out  in: len(tmp_trajectory) of the previous step (0 = None), out: new cutoff_idx
  *                        (= the full course length when nothing collides) -- feed it to mpcb_step as ncourse

@@ -8,7 +8,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MPCB_LIB_PATH") or os.path.join(_HERE, "libmpcb.so")     # override: A/B runs of kernel variants
 CSRC = os.path.join(_HERE, "csrc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-shared", "-Xcompiler", "-fPIC"]
+              "-shared", "-Xcompiler", "-fPIC",
+              "-cudart", "shared"]      # libcudart.so.12 of the image / of torch: no statically linked runtime inside the artefact
 
 
 class MpcbError(RuntimeError):

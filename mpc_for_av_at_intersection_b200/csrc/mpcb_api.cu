@@ -57,9 +57,11 @@ struct mpcb_handle {
             *n_script = nullptr;
         double *script = nullptr, *obs = nullptr;      // scripted cross traffic [B,8,8] and its last get() rows [B,8,6]
         double* pw = nullptr;                          // per-problem cost weights [B,12]
+        double* lam_ws = nullptr;                      // interior-point multipliers of the last solve [B,8,T] (warm start)
         int* vcut = nullptr;                           // mpc_with_speed cutoff_idx [B]
         int *lpt_order = nullptr, *lpt_rank = nullptr, *lpt_hist = nullptr;   // longest-first launch order (mpcb_step.cuh)
         bool hasL = false, has_script = false, has_pw = false, has_vcut = false;
+        std::vector<int> route_host;                   // host copy of the routes: the host-array entry points validate indices against it
         size_t pin_state = 0, pin_diai = 0, pin_status = 0, pin_total = 0;
     } ses;
 };
@@ -431,6 +433,14 @@ int mpcb_step_host(mpcb_handle* h, int B, const double* state, const int* route,
         h->err = "mpcb_step_host: bad arguments"; return MPCB_EINVAL;
     }
     const int T = h->cfg.T;
+    if (!h->courses_dev) { h->err = "mpcb_step_host: no courses set"; return MPCB_EINVAL; }
+    for (int b = 0; b < B; ++b) {        // a bad index would become an out-of-bounds read inside the kernel
+        const int r = route[b];
+        if (r < 0 || r >= h->R || ncourse[b] < 1 || ncourse[b] > h->len_host[r] || target_ind[b] < 0) {
+            h->err = "mpcb_step_host: problem " + std::to_string(b) + ": route id, ncourse (1..course length) or target_ind (>= 0) out of range";
+            return MPCB_EINVAL;
+        }
+    }
     CUDA_TRY(h, cudaSetDevice(h->device));
     const StageLayout lm = stage_layout(h->max_batch, T);
     if (!h->stage.pinned) {
@@ -528,7 +538,7 @@ int session_alloc(mpcb_handle* h) {
                  o_tgt = put(4 * B), o_warm = put(4 * B), o_iters = put(4 * B),
                  o_done = put(4 * B), o_aidx = put(4 * B), o_coll = put(4 * B), o_cidx = put(4 * B),
                  o_nscr = put(4 * B), o_script = put(8 * 8 * MPCB_CP_MAX_OBS * B), o_obs = put(8 * 6 * MPCB_CP_MAX_OBS * B),
-                 o_pw = put(8 * 12 * B), o_vcut = put(4 * B), o_lord = put(4 * B), o_lrank = put(4 * B), o_lhist = put(4 * 65);
+                 o_pw = put(8 * 12 * B), o_lam = put(8 * 8 * T * B), o_vcut = put(4 * B), o_lord = put(4 * B), o_lrank = put(4 * B), o_lhist = put(4 * 65);
     CUDA_TRY(h, cudaMalloc(&s.slab, o));
     CUDA_TRY(h, cudaMemset(s.slab, 0, o));
     char* d = s.slab;
@@ -539,7 +549,7 @@ int session_alloc(mpcb_handle* h) {
     s.status = (int*)(d + o_status); s.iters = (int*)(d + o_iters); s.done = (int*)(d + o_done);
     s.agent_idx = (int*)(d + o_aidx); s.collided = (int*)(d + o_coll); s.coll_idx = (int*)(d + o_cidx);
     s.n_script = (int*)(d + o_nscr); s.script = (double*)(d + o_script); s.obs = (double*)(d + o_obs);
-    s.pw = (double*)(d + o_pw); s.vcut = (int*)(d + o_vcut);
+    s.pw = (double*)(d + o_pw); s.vcut = (int*)(d + o_vcut); s.lam_ws = (double*)(d + o_lam);
     s.lpt_order = (int*)(d + o_lord); s.lpt_rank = (int*)(d + o_lrank); s.lpt_hist = (int*)(d + o_lhist);
     o = 0;
     s.pin_state = put(8 * 4 * B); s.pin_diai = put(8 * 2 * B); s.pin_status = put(4 * B);
@@ -555,6 +565,8 @@ StepParams session_params(mpcb_handle* h) {
     p.target_ind = s.target; p.warm = s.warm; p.oa = s.oa; p.od = s.od; p.traj = s.traj; p.xref = s.xref;
     p.di_ai = s.di_ai; p.xdev = s.xdev; p.status = s.status; p.iters = s.iters;
     p.pw = s.has_pw ? s.pw : nullptr; p.vcut = s.has_vcut ? s.vcut : nullptr;
+    static const bool ipm_warm = !(getenv("MPCB_IPM_WARM") && atoi(getenv("MPCB_IPM_WARM")) == 0);
+    p.lam_ws = ipm_warm ? s.lam_ws : nullptr;
     // longest-first launch order: pays while the launch is MORE than one and no more than a dozen waves of resident warps
     // (8 per SM).  Measured with / without: B = 1024 (under one wave: order is irrelevant, the ordering pass is pure latency)
     // 4.27 / 4.54 M solves/s, 4096: 8.07 / 7.58, 8192: 8.83 / 8.53, 16384: 9.23 / 9.13, 32768: 9.44 / 9.45, 65536: 9.54 / 9.74
@@ -585,7 +597,11 @@ int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* 
         if (nc[b] < 1 || nc[b] > h->len_host[r]) { h->err = "mpcb_session_begin: ncourse out of range"; return MPCB_EINVAL; }
         goal[2 * b] = h->goal_host[2 * r]; goal[2 * b + 1] = h->goal_host[2 * r + 1];
     }
+    if (target_ind_host)
+        for (int b = 0; b < B; ++b)
+            if (target_ind_host[b] < 0) { h->err = "mpcb_session_begin: target_ind must be >= 0"; return MPCB_EINVAL; }
     s.B = B; s.hasL = L_host != nullptr; s.has_script = false; s.has_pw = false; s.has_vcut = false;
+    s.route_host.assign(route_host, route_host + B);
     cudaStream_t st = h->own_stream;
     CUDA_TRY(h, cudaMemcpyAsync(s.route, route_host, 4 * (size_t)B, cudaMemcpyHostToDevice, st));
     CUDA_TRY(h, cudaMemcpyAsync(s.ncourse, nc.data(), 4 * (size_t)B, cudaMemcpyHostToDevice, st));
@@ -614,6 +630,10 @@ int mpcb_session_begin(mpcb_handle* h, int B, const int* route_host, const int* 
 
 int mpcb_session_set_ncourse_host(mpcb_handle* h, const int* ncourse_host) {
     if (!h || !ncourse_host || h->ses.B <= 0) { if (h) h->err = "mpcb_session_set_ncourse_host: no session"; return MPCB_EINVAL; }
+    for (int b = 0; b < h->ses.B; ++b)
+        if (ncourse_host[b] < 1 || ncourse_host[b] > h->len_host[h->ses.route_host[b]]) {
+            h->err = "mpcb_session_set_ncourse_host: problem " + std::to_string(b) + ": ncourse outside 1..course length"; return MPCB_EINVAL;
+        }
     CUDA_TRY(h, cudaSetDevice(h->device));
     if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
     CUDA_TRY(h, cudaMemcpyAsync(h->ses.ncourse, ncourse_host, 4 * (size_t)h->ses.B, cudaMemcpyHostToDevice, h->own_stream));
@@ -642,7 +662,11 @@ int mpcb_session_set_speed_cutoff_host(mpcb_handle* h, const int* cutoff_idx_hos
     CUDA_TRY(h, cudaSetDevice(h->device));
     if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
     if (!cutoff_idx_host) { s.has_vcut = false; return MPCB_OK; }
-    CUDA_TRY(h, cudaMemcpyAsync(s.vcut, cutoff_idx_host, 4 * (size_t)s.B, cudaMemcpyHostToDevice, h->own_stream));
+    // 999 is the reference's "no cut" sentinel (mpc_with_speed.py:276,281), not an index: a course longer than 999 points keeps
+    // its speed reference past point 999
+    std::vector<int> cut(cutoff_idx_host, cutoff_idx_host + s.B);
+    for (int& c : cut) if (c == 999 || c < 0) c = 0x7fffffff;
+    CUDA_TRY(h, cudaMemcpyAsync(s.vcut, cut.data(), 4 * (size_t)s.B, cudaMemcpyHostToDevice, h->own_stream));
     CUDA_TRY(h, cudaStreamSynchronize(h->own_stream));
     s.has_vcut = true;
     return MPCB_OK;
@@ -745,6 +769,16 @@ int mpcb_session_store_host(mpcb_handle* h, int what, const void* src, long long
     void* dst = mpcb_session_device_ptr(h, what);
     const size_t need = field_bytes(h, what);
     if (!dst || need == 0 || (size_t)bytes != need) { h->err = "mpcb_session_store_host: unknown field or wrong size"; return MPCB_EINVAL; }
+    if (what == MPCB_F_ROUTE || what == MPCB_F_NCOURSE || what == MPCB_F_TARGET) {      // indices the kernels trust
+        const int* v = (const int*)src;
+        auto& rh = h->ses.route_host;
+        for (int b = 0; b < h->ses.B; ++b) {
+            const bool ok = what == MPCB_F_ROUTE ? (v[b] >= 0 && v[b] < h->R)
+                          : what == MPCB_F_NCOURSE ? (v[b] >= 1 && v[b] <= h->len_host[rh[b]]) : v[b] >= 0;
+            if (!ok) { h->err = "mpcb_session_store_host: problem " + std::to_string(b) + ": index out of range"; return MPCB_EINVAL; }
+        }
+        if (what == MPCB_F_ROUTE) rh.assign(v, v + h->ses.B);
+    }
     CUDA_TRY(h, cudaSetDevice(h->device));
     if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));   // order after asynchronous session work
     CUDA_TRY(h, cudaMemcpyAsync(dst, src, need, cudaMemcpyHostToDevice, h->own_stream));

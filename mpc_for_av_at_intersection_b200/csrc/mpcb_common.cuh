@@ -47,6 +47,8 @@ struct StepParams {
                              //   interior-point iterations each problem just needed (a good predictor of the next step's)
     int* lpt_rank;           // [B] scratch: (bin << 24) | rank inside the bin
     int* lpt_hist;           // [65] scratch: 64 bins (bin 0 = most iterations) + the finished-warp counter; zero between launches
+    // interior-point warm start across control steps (resident sessions only): the multipliers of the previous solve
+    double* lam_ws;          // [B][8][T] io or null: slot-major rows of the 8 constraint slots per stage
 #ifdef MPCB_TRACE
     double* trace;           // development builds only: [B][128][8] per-iteration log (it, res_d, res_p, mu, alpha, flags, ., .)
 #endif

@@ -102,7 +102,10 @@ __global__ void __launch_bounds__(WARPS * 32) coupling_kernel(const CouplingPara
     if (ncp > 0) upd = (cx[aidx] != cx[ncp - 1]) || (cy[aidx] != cy[ncp - 1]) || (cyaw[aidx] != cyaw[ncp - 1]);
     if (upd) {
         const int ni = nearest_index_in_direction(cx, cy, aidx, ncf, x0, y0, lane);
-        if (ni < 0) { if (lane == 0 && p.flags) p.flags[b] = 1; return; }      // the reference raises (trajectories.py:120)
+        if (ni < 0) {      // the reference raises (trajectories.py:120): the ego is dead from here on, like MPCB_ST_NEAREST in the step kernel
+            if (lane == 0) { if (p.flags) p.flags[b] = 1; if (p.done) p.done[b] = 2; }
+            return;
+        }
         aidx = ni;
     }
     const int n = ncf - aidx;                                      // len(trajectory_full[traj_agent_idx:]) >= 1

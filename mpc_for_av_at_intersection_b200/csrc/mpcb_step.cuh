@@ -69,6 +69,7 @@ struct WarpSmem {
 // Critical path of one step: publish column -> barrier -> broadcast loads -> FMAs.  The reciprocal of the NEXT
 // pivot is computed by its owner as soon as the first FMA of the update has produced it, i.e. in the shadow of the
 // remaining FMAs, and published together with the column (a0 / iv carry it from step to step).
+// [phase: ldl accel steps]
 template <int T, int JMAX>
 __device__ __forceinline__ void ldl_accel_steps(WarpSmem<T>& sm, double (&R)[T], double (&Q)[T], int k0, int k1, int lane,
                                                 double wv_suf, double dA, double& ra, double& rdl, bool& bad,
@@ -107,6 +108,7 @@ __device__ __forceinline__ void ldl_accel_steps(WarpSmem<T>& sm, double (&R)[T],
     }
 }
 
+// [phase: ldl steer steps]
 template <int T, int JMAX>
 __device__ __forceinline__ void ldl_steer_steps(WarpSmem<T>& sm, double (&C)[T], int k0, int k1, int lane, bool act,
                                                 double dC, double wr_prev, double& rdl, bool& bad, double& invd,
@@ -148,6 +150,7 @@ __device__ __forceinline__ void ldl_steer_steps(WarpSmem<T>& sm, double (&C)[T],
 // from register fragments: A -= L U', B -= L21 U' with L = scaled panel rows, U = unscaled ones.  Compared with the
 // lane-per-row rank-1 updates this removes the operand broadcast through the LSU (one wavefront per double) and
 // issues 256 FMAs per instruction.
+// [phase: accel blocked dmma]
 template <int T>
 __device__ __forceinline__ void ldl_accel_blocked(WarpSmem<T>& sm, int lane, bool act, double wv_suf, double dA,
                                                   double& ra, double& rdl, bool& bad, double& inva) {
@@ -264,6 +267,7 @@ __device__ __forceinline__ void ldl_accel_blocked(WarpSmem<T>& sm, int lane, boo
     }
 }
 
+// [phase: nearest idx]
 // top-3 insertion keeping (d, idx) ascending; ties keep the earlier (lower) index first
 __device__ __forceinline__ void top3_insert(double d, int i, double (&bd)[3], int (&bi)[3]) {
     if (d < bd[2]) {
@@ -318,6 +322,7 @@ __device__ __forceinline__ int nearest_index_in_direction(const double* __restri
 
 namespace mpcb {
 
+// [phase: G ops]
 // ---- structured constraint operator ------------------------------------------------------------
 // slots per stage t: 0: a<=amax  1: -a<=-amin  2: d<=smax  3: -d<=smax
 //                    4: d[t+1]-d[t]<=r  5: -(d[t+1]-d[t])<=r  (t<=T-2)   6: v[t+1]<=vmax  7: -v[t+1]<=-vmin
@@ -336,6 +341,7 @@ __device__ __forceinline__ void GT_apply(const double (&y)[8], double dt, int la
     gd = y[2] - y[3] - r + shfl_up1(r, lane);
 }
 
+// [phase: kernel head/inputs]
 // returns the interior-point iterations the problem took (0 if it was skipped)
 template <int T, int WARPS, bool VAR>
 __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
@@ -385,6 +391,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
     double xr_x = 0.0, xr_y = 0.0, xr_yaw = 0.0;       // xref at state index lane (0..T)
 
     for (int pass = 0; pass < p.max_iter; ++pass) {
+        // [phase: A2]
         // ---- A2: reference lookup -----------------------------------------------------------------
         const int ni = nearest_index_in_direction(cx, cy, tind, nc, x0, y0, lane);
         if (ni < 0) { status = MPCB_ST_NEAREST; break; }
@@ -416,6 +423,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
         if constexpr (VAR) xr_v = idx < vcut ? p.ref_speed : 0.0;
         const bool reach = (idx == nc - 1);
 
+        // [phase: A3]
         // ---- A3: rollout of the previous (unshifted) solution: operating point (vbar, phibar) -------
         const double dcl = clampd(od, -p.max_steer, p.max_steer);
         const double tnd = act ? tan(dcl) : 0.0;
@@ -434,6 +442,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
             if (lane == t + 1) pb = pcur;
         }
 
+        // [phase: A4/A5]
         // ---- A4: linearisation coefficients of stage `lane` -----------------------------------------
         double sn, cs;
         sincos(pb, &sn, &cs);
@@ -464,6 +473,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
         const double ra_w = act ? (reach ? p.r_end : R0) : 0.0;     // mpc.py:177-180
         const double rd_w = act ? (reach ? p.r_end : R1) : 0.0;
 
+        // [phase: H build]
         // ---- condensed Hessian from suffix moments ----------------------------------------------------
         const double Zx = scan_up(c_, lane), Zy = scan_up(s_, lane);
         const double Wx = scan_up(-pp, lane), Wy = scan_up(qq, lane);
@@ -519,6 +529,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
         }
         __syncwarp();
         auto tld = [&](int i) { return act ? sm.tab[i][lane] : 0.0; };
+        // [phase: predict/grad defs]
         // ---- linear prediction and objective gradient by scans ------------------------------------------
         // returns the states at index lane+1 (lanes < T); see oracle/condensed_model.py states()/grad()
         auto predict = [&](double a, double d, double& xs, double& ys, double& vs, double& phs) {
@@ -554,6 +565,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
             gd = act ? bb * pph + 2.0 * rd_w * d + 2.0 * Rd1 * fd : 0.0;
         };
 
+        // [phase: ipm init + grad matvec]
         // ---- A6: interior point on  min J(u)  s.t.  G u <= h ----------------------------------------------
         double hh8[8];
         hh8[0] = p.max_accel; hh8[1] = -p.max_decel; hh8[2] = p.max_steer; hh8[3] = p.max_steer;
@@ -582,11 +594,20 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
                 s[c] = mk[c] ? fmax(hh8[c] - g[c], 1.0) : 1.0;
-#ifdef MPCB_AB_LEGACY_START
-                lam[c] = mk[c] ? 1.0 : 0.0;
-#else
                 lam[c] = mk[c] ? mu0 * rcp(s[c]) : 0.0;
-#endif
+            }
+            // Resident sessions: the multipliers of the previous control step's solve, floored at 1 (the next QP is the same
+            // problem one stage on, so the active rows keep their multipliers; everything else restarts from 1).  The
+            // optimum is unique, the answer does not depend on the start -- only the iteration count does: 9.15 -> 8.13
+            // per solve on the bench loop (numpy twin, profiles/r02_NOTES.md).
+            if (p.lam_ws && warm && pass == 0) {
+                const double* __restrict__ lw = p.lam_ws + (size_t)b * 8 * T;
+                const double fl = fmax(1.0, 1e-5 * gscale);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const double lp = act ? lw[c * T + lane] : 0.0;
+                    lam[c] = mk[c] ? fmax(lp, fl) : 0.0;
+                }
             }
         }
         // gradient inside the interior-point loop: g0 + H u from the stored cost Hessian (column j of every block is
@@ -632,6 +653,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
         // Two nested loops so that the residual evaluation (gradient mat-vec, G and G' scans: ~6 KB of code that runs two to
         // four times per solve) sits OUTSIDE the address range of the hot iteration loop, which is as large as the 32 KB
         // instruction cache: the inner loop leaves ("break") whenever it needs fresh residuals and the outer one re-enters it.
+        // [phase: residuals (outer loop)]
         bool stop = !feasible0;
         while (!stop) {
             {
@@ -656,6 +678,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                     if (act) { sm.bc[6][lane] = a; sm.bc[7][lane] = d; }
                 }
             }
+        // [phase: gap + stopping tests]
         for (;;) {
             {
                 double sl = 0.0;
@@ -678,6 +701,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 break;
             }
 
+            // [phase: W, rhs]
             // ---- M = H + G' W G into registers (rows `lane` of A, B, C) ---------------------------------
             double sinv[8], w[8];
 #pragma unroll
@@ -700,6 +724,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 GT_apply<T>(y, dt, lane, ya, yd);
                 ra = ya - rda; rdl = yd - rdd;
             }
+            // [phase: factor driver+syrk]
             // ---- LDL' of M = H + G'WG, forward solve of the predictor right-hand side fused -------------------
             bool bad = false;
             double inva = 0.0, invd = 0.0;
@@ -815,6 +840,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 break;
             }
             if (!act) { ra = 0.0; rdl = 0.0; }
+            // [phase: solves]
             // Triangular solves with the pivots in rolled loops.  The factor blocks are zero on and above the diagonal,
             // so every step is shuffle -> FMA with no predicate; the running right-hand sides are kept PRE-SCALED by
             // 1/d_i (the coefficient is scaled instead, off the dependency chain), which makes the value a lane
@@ -862,6 +888,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 fa = ga; fd = gd;                              // = D^-1 L^-1 r
             };
 
+            // [phase: predictor+corrector]
             // ---- predictor (ph = 0) and corrector (ph = 1): one copy of the back solve, the G product and the ratio test ----
             // (a rolled two-pass loop: the hot loop body must stay inside the 32 KB instruction cache)
             double dsa[8], dla[8], rc[8];
@@ -934,6 +961,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
             if ((it & 15) == 0 || since >= 2) { since = 0; break; }
         }
         }
+        // [phase: epilogue]
         iters = it;
         // OPTIMAL: the configured tolerances, or -- when the loop ended first -- a verified iterate of at least the 1e-8
         // class that the reference's ECOS calls optimal; INACCURATE: ECOS's reduced class (both accepted, mpc.py:196)
@@ -946,6 +974,11 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
         // solution of this pass: mpc.py:197-202
         solved = true;
         oa = a; od = d;
+        if (p.lam_ws && act) {                           // multipliers for the next control step's start (see above)
+            double* __restrict__ lw = p.lam_ws + (size_t)b * 8 * T;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) lw[c * T + lane] = lam[c];
+        }
         {
             double xs, ys, vs, phs;
             predict(a, d, xs, ys, vs, phs);
@@ -972,6 +1005,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
     const double qnan = __longlong_as_double(0x7ff8000000000000LL);
     if (solved) {
         if (act) { p.oa[(size_t)b * T + lane] = oa; p.od[(size_t)b * T + lane] = od; }
+
         if (p.traj && lane <= T) {
             p.traj[tb + lane] = sx;
             p.traj[tb + (T + 1) + lane] = sy;

@@ -4,5 +4,5 @@
 set -e
 NAME=$1; shift
 D=$(dirname "$0")/../mpc_for_av_at_intersection_b200
-nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -shared -Xcompiler -fPIC "$@" -o $D/libmpcb_$NAME.so $D/csrc/*.cu
+nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -shared -Xcompiler -fPIC -cudart shared "$@" -o $D/libmpcb_$NAME.so $D/csrc/*.cu
 echo built $D/libmpcb_$NAME.so

@@ -17,8 +17,12 @@ data=[r for r in rows[2:] if len(r)==len(hdr) and r[0]!='Address']
 if len(data)!=len(inst_line) and len(data)%len(inst_line)==0: data=data[:len(inst_line)]   # several captures of the same kernel: first one
 assert len(data)==len(inst_line),(len(data),len(inst_line))
 src=open('/root/repo/mpc_for_av_at_intersection_b200/csrc/mpcb_step.cuh').read().split('\n')
-def find(s): return next(i+1 for i,l in enumerate(src) if s in l)
-marks=sorted([(1,'file head'),(find('void ldl_accel_steps'),'ldl accel steps'),(find('void ldl_steer_steps'),'ldl steer steps'),(find('void ldl_accel_blocked'),'accel blocked dmma'),(find('top-3 insertion'),'nearest idx'),(find('structured constraint operator'),'G ops'),(find('void mpc_step_body'),'kernel head/inputs'),(find('A2: reference lookup'),'A2'),(find('A3: rollout'),'A3'),(find('A4: linearisation'),'A4/A5'),(find('condensed Hessian from suffix'),'H build'),(find('linear prediction and objective gradient'),'predict/grad defs'),(find('A6: interior point'),'ipm init + grad matvec'),(find('while (feasible0) {'),'residuals'),(find("M = H + G' W G"),'W, rhs'),(find("LDL' of M = H"),'factor driver+syrk'),(find('Triangular solves with the pivots'),'solves'),(find('---- predictor (ph = 0)'),'predictor+corrector'),(find('iters = it;'),'epilogue')])
+marks=[(1,'file head')]
+for i,l in enumerate(src):
+    m=re.search(r'// \[phase: (.+?)\]',l)
+    if m: marks.append((i+1,m.group(1)))
+if len(marks)<10: sys.exit("ncu_phase.py: the '// [phase: ...]' markers are missing from mpcb_step.cuh -- refusing to write a table")
+marks.sort()
 agg=defaultdict(lambda:[0,0,0,defaultdict(int)])
 for l,op,r in zip(inst_line,ops,data):
     name='?'

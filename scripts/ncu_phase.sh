@@ -13,5 +13,5 @@ st=[i for i,l in enumerate(L) if l.startswith('.text.') and sys.argv[2] in l][0]
 en=[i for i,l in enumerate(L) if l.startswith('.text.') and i>st]
 print('\n'.join(L[st-8:(en[0]-8 if en else len(L))]))
 PY
-python scripts/ncu_phase.py $W/dis.txt $W/sass.csv $NP
-echo "workdir $W"
+python scripts/ncu_phase.py $W/dis.txt $W/sass.csv $NP > $W/table.txt   # set -e: a failure prints nothing (no traceback posing as a table)
+cat $W/table.txt
