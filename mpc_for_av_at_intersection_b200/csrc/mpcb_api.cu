@@ -176,7 +176,7 @@ int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st);
 template <int NT, int MINB = 1>
 int launch_step_long_nt(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     const int T = h->cfg.T;
-    if (T + 1 > NT) { h->err = "mpcb: horizon too long for the CTA-per-problem kernel"; return MPCB_EINVAL; }
+    if (T + 1 > NT || T % 4 != 0) { h->err = "mpcb: the CTA-per-problem kernel needs T + 1 <= threads and T a multiple of 4 (8x8 tiles)"; return MPCB_EINVAL; }
     const size_t smem = mpcb::LongSmem::bytes(T, NT);
     auto kern = mpcb::mpc_step_long_kernel<NT, MINB>;
     static thread_local int configured_dev = -1;
@@ -196,9 +196,17 @@ int launch_step_long_nt(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
 // 248-register CTAs per SM either way) is faster with 4 (157 K vs 118 K).  Also measured and rejected: 512 threads at 128
 // registers (spills; 27.0 K at T = 80), register caps for 3 or 4 CTAs per SM at T = 40 (135 K / 162 K with spills).
 int launch_step_long(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
+    // threads per problem (MPCB_LONG_THREADS overrides, tuning only): rows of the system matrix go to threads i % NT
     static const int nt_env = getenv("MPCB_LONG_THREADS") ? atoi(getenv("MPCB_LONG_THREADS")) : 0;
-    const bool wide = nt_env ? nt_env == 256 : h->cfg.T > 40;
-    return wide ? launch_step_long_nt<256>(h, p, st) : launch_step_long_nt<kLongThreads>(h, p, st);
+    static const int minb = getenv("MPCB_LONG_MINB") ? atoi(getenv("MPCB_LONG_MINB")) : 0;     // resident CTAs per SM asked of ptxas
+    const int nthreads = nt_env ? nt_env : (h->cfg.T > 40 ? 256 : 64);
+    if (nthreads == 256) return launch_step_long_nt<256>(h, p, st);
+    if (nthreads == 64) return launch_step_long_nt<64, 4>(h, p, st);
+    switch (minb) {
+        case 2: return launch_step_long_nt<kLongThreads, 2>(h, p, st);
+        case 3: return launch_step_long_nt<kLongThreads, 3>(h, p, st);
+        default: return launch_step_long_nt<kLongThreads>(h, p, st);
+    }
 }
 
 #ifdef MPCB_TRACE

@@ -18,6 +18,7 @@
 
 namespace mpcb {
 
+// [phase: block primitives]
 template <int NT>
 struct BlockOps {
     static constexpr int NW = NT / 32;
@@ -144,33 +145,42 @@ __device__ __forceinline__ int nearest_index_block(BlockOps<NT>& bo, const doubl
     return -1;
 }
 
-// shared-memory carve-up of one problem (doubles): M packed lower row-major, then the per-stage tables
+// shared-memory carve-up of one problem (doubles).  The system matrix M = H + G'WG (n = 2T unknowns, n a multiple of 8) is
+// kept as its LOWER 8x8 tiles, tile (I, J <= I) at M + (I (I + 1) / 2 + J) * 64, row-major inside a tile: a tile is the
+// accumulator fragment of one mma.m8n8k4 (lane l <-> elements [l/4][2 (l%4)], [l/4][2 (l%4) + 1]: one conflict-free 16-byte
+// access per lane), a row chunk of a tile is what one thread of the lane-per-row phases reads.
 struct LongSmem {
-    int T, n;
-    double* M;        // n (n + 1) / 2
+    int T, n, nt;
+    double* M;        // nt (nt + 1) / 2 tiles x 64
+    double* Dinv;     // nt x 64: inverses of the unit-lower diagonal tiles of L (zero above the diagonal)
+    double* Lp;       // n x 4: -L of the current 4-column panel (rows above the trailing block are zero): A fragments
+    double* Wp;       // n x 4:  L D of the current panel (same zero rows): B fragments
     double* vec;      // n      right-hand side / solution
-    double* dinv;     // n
-    double* colb;     // n      unscaled pivot column
+    double* dinv;     // n      1 / d_k
     double* tab;      // NTAB x (T + 1) per-stage tables
     double* red;      // scratch of the block primitives
     int* redi;
     static constexpr int NTAB = 24;
     __host__ __device__ static size_t bytes(int T, int NT) {
-        const size_t n = 2 * (size_t)T;
-        return (n * (n + 1) / 2 + 3 * n + (size_t)NTAB * (T + 1) + NT / 32 + 4) * sizeof(double) + (NT / 32 + 4) * sizeof(int);
+        const size_t n = 2 * (size_t)T, nt = n / 8;
+        return (nt * (nt + 1) / 2 * 64 + nt * 64 + 8 * n + 2 * n + (size_t)NTAB * (T + 1) + NT / 32 + 4) * sizeof(double) +
+               (NT / 32 + 4) * sizeof(int);
     }
     __device__ __forceinline__ void carve(unsigned char* raw, int T_, int NT) {
-        T = T_; n = 2 * T_;
+        T = T_; n = 2 * T_; nt = n >> 3;
         double* q = reinterpret_cast<double*>(raw);
-        M = q; q += (size_t)n * (n + 1) / 2;
+        M = q; q += (size_t)nt * (nt + 1) / 2 * 64;
+        Dinv = q; q += (size_t)nt * 64;
+        Lp = q; q += 4 * n;
+        Wp = q; q += 4 * n;
         vec = q; q += n;
         dinv = q; q += n;
-        colb = q; q += n;
         tab = q; q += (size_t)NTAB * (T + 1);
         red = q; q += NT / 32 + 4;
         redi = reinterpret_cast<int*>(q);
     }
     __device__ __forceinline__ double* t(int i) const { return tab + (size_t)i * (T + 1); }
+    __device__ __forceinline__ double* tile(int I, int J) const { return M + ((I * (I + 1) >> 1) + J) * 64; }
 };
 
 
@@ -178,6 +188,7 @@ struct LongSmem {
 enum { LT_OA = 0, LT_TERM, LT_ZX, LT_ZY, LT_WX, LT_WY, LT_BB, LT_HH, LT_GAX, LT_GAY, LT_GCX, LT_GCY, LT_HA, LT_HC, LT_HB,
        LT_DGA, LT_DGC, LT_WVS, LT_DA, LT_DC, LT_WRP, LT_U0, LT_U1, LT_SPARE };
 
+// [phase: kernel head/inputs]
 template <int NT, int MINB = 1>
 __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParams p, const int T) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -229,9 +240,9 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
     bool solved = false, have_ov = false;
     double sx = 0.0, sy = 0.0, sv = 0.0, sph = 0.0;    // solution states at index tid (0..T)
     double xr_x = 0.0, xr_y = 0.0, xr_yaw = 0.0;       // xref at state index tid (0..T)
-    auto idx = [](int i, int j) { return i * (i + 1) / 2 + j; };
 
     for (int pass = 0; pass < p.max_iter; ++pass) {
+        // [phase: A2 A3 A4 A5 tables]
         // ---- A2: reference lookup (main/lib/mpc.py:86-109) ------------------------------------------------
         const int ni = nearest_index_block<NT>(bo, cx, cy, tind, nc, x0, y0);
         if (ni < 0) { status = MPCB_ST_NEAREST; break; }
@@ -341,6 +352,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             __syncthreads();
         }
 
+        // [phase: predict/grad/G defs]
         // ---- linear prediction and objective gradient by scans (oracle/condensed_model.py states()/grad()) ----
         auto predict = [&](double a, double d, double& xs, double& ys, double& vs, double& phs) {
             const double sa = bo.scan_up(a);
@@ -383,6 +395,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             gd = y[2] - y[3] - r + bo.up1(r);
         };
 
+        // [phase: ipm init]
         // ---- A6: interior point on  min J(u)  s.t.  G u <= h -------------------------------------------------
         double hh8[8];
         hh8[0] = p.max_accel; hh8[1] = -p.max_decel; hh8[2] = p.max_steer; hh8[3] = p.max_steer;
@@ -410,6 +423,15 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                 s[c] = mk[c] ? fmax(hh8[c] - g[c], 1.0) : 1.0;
                 lam[c] = mk[c] ? mu0 * rcp(s[c]) : 0.0;
             }
+            if (p.lam_ws && warm && pass == 0) {        // multipliers of the previous control step's solve, floored (mpcb_step.cuh)
+                const double* __restrict__ lw = p.lam_ws + (size_t)b * 8 * T;
+                const double fl = fmax(1.0, 1e-5 * gscale);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const double lp = act ? lw[c * T + tid] : 0.0;
+                    lam[c] = mk[c] ? fmax(lp, fl) : 0.0;
+                }
+            }
         }
         double res_d = 1e300, res_p = 1e300, mu = 1e300;
         bool converged = false;
@@ -417,6 +439,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
         double mu_prev = 1e300;
         bool eta_safe = false;
         double best_m = 1e300, best_a = 0.0, best_d = 0.0;      // best iterate so far and its merit, see mpcb_step.cuh
+        // [phase: residuals + tests]
         while (feasible0) {
             double rda, rdd, rp[8];
             {
@@ -449,6 +472,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) { converged = true; break; }
             if (it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) break;
 
+            // [phase: W, rhs]
             double sinv[8], w[8];
 #pragma unroll
             for (int c = 0; c < 8; ++c) { sinv[c] = rcp(s[c]); w[c] = lam[c] * sinv[c]; }
@@ -470,56 +494,129 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                 if (act) { sm.vec[tid] = ya - rda; sm.vec[T + tid] = yd - rdd; }
             }
             __syncthreads();
-            // ---- assemble M = H + G'WG (packed lower, row-major; unknowns a_0..a_{T-1}, d_0..d_{T-1}) ---------
+            // [phase: assemble M]
+            // ---- assemble M = H + G'WG tile by tile (unknowns a_0..a_{T-1}, d_0..d_{T-1}; T is a multiple of 4, so a tile
+            //      lies inside one of the three blocks): lane l writes elements [l/4][2 (l%4)], [l/4][2 (l%4) + 1] ----------
             {
                 const double kA = 2.0 * dt * dt;
-                for (int i = wid; i < n; i += NW) {
-                    double* row = sm.M + idx(i, 0);
-                    if (i < T) {                                   // accel row i, accel columns j <= i
-                        const double hA = sm.t(LT_HA)[i], gAx = sm.t(LT_GAX)[i], gAy = sm.t(LT_GAY)[i], wvs = sm.t(LT_WVS)[i];
-                        for (int j = lane; j <= i; j += 32) {
-                            double v = kA * (hA + sm.t(LT_ZX)[j] * gAx + sm.t(LT_ZY)[j] * gAy) + wvs;
-                            if (j == i) v += sm.t(LT_DGA)[i] + sm.t(LT_DA)[i];
-                            if (j == i - 1) v -= 2.0 * Rd0;
-                            row[j] = v;
+                const int er = lane >> 2, ec = (lane & 3) * 2;
+                const int tT = T >> 3;                             // accel tiles per side
+                for (int I = wid; I < sm.nt; I += NW) {
+                    const int i = 8 * I + er;
+                    for (int J = 0; J <= I; ++J) {
+                        double v[2];
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int j = 8 * J + ec + e;
+                            double x = 0.0;
+                            if (I < tT) {                          // accel row i, accel column j
+                                x = kA * (sm.t(LT_HA)[i] + sm.t(LT_ZX)[j] * sm.t(LT_GAX)[i] + sm.t(LT_ZY)[j] * sm.t(LT_GAY)[i]) + sm.t(LT_WVS)[i];
+                                if (j == i) x += sm.t(LT_DGA)[i] + sm.t(LT_DA)[i];
+                                if (j == i - 1) x -= 2.0 * Rd0;
+                            } else {
+                                const int r = i - T;
+                                const double bbr = sm.t(LT_BB)[r];
+                                if (J < tT) {                      // steer row r, accel column j
+                                    const double Blo = sm.t(LT_HB)[r] + sm.t(LT_ZX)[j] * sm.t(LT_GCX)[r] + sm.t(LT_ZY)[j] * sm.t(LT_GCY)[r];
+                                    const double Bup = sm.t(LT_HH)[j] + sm.t(LT_WX)[r] * sm.t(LT_GAX)[j] + sm.t(LT_WY)[r] * sm.t(LT_GAY)[j];
+                                    x = 2.0 * bbr * dt * ((j <= r) ? Blo : Bup);
+                                } else {                           // steer row r, steer column q
+                                    const int q = j - T;
+                                    x = 2.0 * bbr * sm.t(LT_BB)[q] * (sm.t(LT_HC)[r] + sm.t(LT_WX)[q] * sm.t(LT_GCX)[r] + sm.t(LT_WY)[q] * sm.t(LT_GCY)[r]);
+                                    if (q == r) x += sm.t(LT_DGC)[r] + sm.t(LT_DC)[r];
+                                    if (q == r - 1) x -= 2.0 * Rd1 + sm.t(LT_WRP)[r];
+                                }
+                            }
+                            v[e] = (j <= i) ? x : 0.0;             // strictly upper part of the diagonal tiles: never read
                         }
-                    } else {                                       // steer row r = i - T
-                        const int r = i - T;
-                        const double bbr = sm.t(LT_BB)[r], kB = 2.0 * bbr * dt, kC = 2.0 * bbr;
-                        const double hB = sm.t(LT_HB)[r], hC = sm.t(LT_HC)[r], gCx = sm.t(LT_GCX)[r], gCy = sm.t(LT_GCY)[r];
-                        const double Wxr = sm.t(LT_WX)[r], Wyr = sm.t(LT_WY)[r];
-                        for (int j = lane; j < T; j += 32) {       // cross block: accel column j
-                            const double Blo = hB + sm.t(LT_ZX)[j] * gCx + sm.t(LT_ZY)[j] * gCy;
-                            const double Bup = sm.t(LT_HH)[j] + Wxr * sm.t(LT_GAX)[j] + Wyr * sm.t(LT_GAY)[j];
-                            row[j] = kB * ((j <= r) ? Blo : Bup);
-                        }
-                        for (int j = lane; j <= r; j += 32) {      // steer block: steer column j <= r
-                            double v = kC * sm.t(LT_BB)[j] * (hC + sm.t(LT_WX)[j] * gCx + sm.t(LT_WY)[j] * gCy);
-                            if (j == r) v += sm.t(LT_DGC)[r] + sm.t(LT_DC)[r];
-                            if (j == r - 1) v -= 2.0 * Rd1 + sm.t(LT_WRP)[r];
-                            row[T + j] = v;
-                        }
+                        *reinterpret_cast<double2*>(sm.tile(I, J) + er * 8 + ec) = make_double2(v[0], v[1]);
                     }
                 }
             }
-            // ---- LDL' in place (right-looking): column k is scaled, the trailing rows go to the warps -----------
+            // [phase: panel factor]
+            // ---- blocked right-looking LDL' in place, panels of 4 columns ------------------------------------------------
+            // Per panel: (1) every thread factors the 4x4 pivot block redundantly in registers (broadcast reads, no barrier, no
+            // pivot round trip), the thread of row i forward-substitutes its own four entries, stores L in place and drops
+            // -L and L D into the fragment buffers; (2) the trailing lower tiles get their rank-4 update on the FP64 tensor
+            // cores, M(I,J) -= L(I,:) (L D)(J,:)': one mma.m8n8k4 per tile, accumulator read and written with one 16-byte access
+            // per lane, tile rows dealt to the warps in pairs of equal total length.  Two barriers per FOUR pivots.
             bool bad = false;
-            for (int k = 0; k < n; ++k) {
+            for (int k = 0; k < n; k += 4) {
                 __syncthreads();
-                const double dk = sm.M[idx(k, k)];
-                bad = bad || !(dk > 0.0);
-                const double iv = rcp(dk);
-                for (int i = k + 1 + tid; i < n; i += NT) {
-                    const double v = sm.M[idx(i, k)];
-                    sm.colb[i] = v;
-                    sm.M[idx(i, k)] = v * iv;
+                const int Kt = k >> 3, ko = k & 7;
+                const double* Dg = sm.tile(Kt, Kt) + ko * 8 + ko;
+                const double m00 = Dg[0], m10 = Dg[8], m11 = Dg[9], m20 = Dg[16], m21 = Dg[17], m22 = Dg[18],
+                             m30 = Dg[24], m31 = Dg[25], m32 = Dg[26], m33 = Dg[27];
+                const double i0 = rcp(m00);
+                const double l10 = m10 * i0, l20 = m20 * i0, l30 = m30 * i0;
+                const double d1 = m11 - l10 * m10, w21 = m21 - l20 * m10, w31 = m31 - l30 * m10;
+                const double i1 = rcp(d1);
+                const double l21 = w21 * i1, l31 = w31 * i1;
+                const double d2 = m22 - l20 * m20 - l21 * w21, w32 = m32 - l30 * m20 - l31 * w21;
+                const double i2 = rcp(d2);
+                const double l32 = w32 * i2;
+                const double d3 = m33 - l30 * m30 - l31 * w31 - l32 * w32;
+                const double i3 = rcp(d3);
+                bad = bad || !(m00 > 0.0 && d1 > 0.0 && d2 > 0.0 && d3 > 0.0 && i0 < 1e300 && i1 < 1e300 && i2 < 1e300 && i3 < 1e300);
+                for (int i = tid; i < n; i += NT) {                 // row i of the panel (threads take rows i, i + NT, ...)
+                    if (i < k) continue;
+                    double2* lp = reinterpret_cast<double2*>(sm.Lp + 4 * i);
+                    double2* wp = reinterpret_cast<double2*>(sm.Wp + 4 * i);
+                    if (i >= k + 4) {
+                        double2* row = reinterpret_cast<double2*>(sm.tile(i >> 3, Kt) + (i & 7) * 8 + ko);
+                        const double2 r01 = row[0], r23 = row[1];
+                        const double w0 = r01.x, l0 = w0 * i0;
+                        const double w1 = r01.y - l0 * m10, l1 = w1 * i1;
+                        const double w2 = r23.x - l0 * m20 - l1 * w21, l2 = w2 * i2;
+                        const double w3 = r23.y - l0 * m30 - l1 * w31 - l2 * w32, l3 = w3 * i3;
+                        row[0] = make_double2(l0, l1); row[1] = make_double2(l2, l3);
+                        lp[0] = make_double2(-l0, -l1); lp[1] = make_double2(-l2, -l3);
+                        wp[0] = make_double2(w0, w1); wp[1] = make_double2(w2, w3);
+                    } else {                                       // rows of the pivot block: nothing left to update
+                        lp[0] = make_double2(0.0, 0.0); lp[1] = make_double2(0.0, 0.0);
+                        wp[0] = make_double2(0.0, 0.0); wp[1] = make_double2(0.0, 0.0);
+                        const int a = i - k;
+                        sm.dinv[i] = a == 0 ? i0 : a == 1 ? i1 : a == 2 ? i2 : i3;
+                    }
                 }
-                if (tid == 0) sm.dinv[k] = iv;
                 __syncthreads();
-                for (int i = k + 1 + wid; i < n; i += NW) {
-                    const double li = sm.colb[i] * iv;
-                    double* row = sm.M + idx(i, 0);
-                    for (int j = k + 1 + lane; j <= i; j += 32) row[j] = fma(-li, sm.colb[j], row[j]);
+                // [phase: trailing update dmma]
+                // the pivot block's own L entries: written now, by the one warp that owns its tile in this phase
+                const int Jmin = (k + 4) >> 3;
+                const int Rr = sm.nt - Jmin;                       // tile rows (= tile columns) of the trailing block
+                auto write_pivot_block = [&]() {
+                    double* Dw = sm.tile(Kt, Kt) + ko * 8 + ko;
+                    Dw[8] = l10; Dw[16] = l20; Dw[17] = l21; Dw[24] = l30; Dw[25] = l31; Dw[26] = l32;
+                };
+                if (ko == 4 && tid == 0) write_pivot_block();      // tile (Kt, Kt) is not part of the trailing block
+                for (int pr = wid; 2 * pr < Rr; pr += NW) {
+#pragma unroll 1
+                    for (int half = 0; half < 2; ++half) {
+                        const int rel = half == 0 ? pr : Rr - 1 - pr;
+                        if (half == 1 && rel == pr) break;
+                        const int I = Jmin + rel;
+                        const double afrag = sm.Lp[(8 * I + (lane >> 2)) * 4 + (lane & 3)];
+                        // four tiles in flight: all loads, then the MMAs, then the stores (the tiles of a row are consecutive
+                        // in memory; the compiler cannot prove that a store to one does not feed the next load)
+                        const double* wj = sm.Wp + (lane >> 2) * 4 + (lane & 3);
+                        double2* Crow = reinterpret_cast<double2*>(sm.tile(I, 0) + (lane >> 2) * 8 + (lane & 3) * 2);
+                        for (int J = Jmin; J <= I; J += 4) {
+                            double bf[4];
+                            double2 c[4];
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) {
+                                const int Ju = min(J + u, I);
+                                bf[u] = wj[32 * Ju];
+                                c[u] = Crow[32 * Ju];
+                            }
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) dmma_m8n8k4(c[u].x, c[u].y, afrag, bf[u]);
+#pragma unroll
+                            for (int u = 0; u < 4; ++u)
+                                if (J + u <= I) Crow[32 * (J + u)] = c[u];
+                        }
+                        if (ko == 0 && I == Kt) { __syncwarp(); if (lane == 0) write_pivot_block(); }
+                    }
                 }
             }
             __syncthreads();
@@ -527,23 +624,84 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             if (p.trace && tid == 0 && it < 128 && bad) p.trace[((size_t)b * 128 + it) * 8 + 6] = 1.0;
 #endif
             if (bad) break;
-            // L D L' x = vec, in place
-            auto solve = [&]() {
-                for (int k = 0; k < n - 1; ++k) {                  // forward, column oriented
-                    const double yk = sm.vec[k];
-                    for (int i = k + 1 + tid; i < n; i += NT) sm.vec[i] = fma(-sm.M[idx(i, k)], yk, sm.vec[i]);
-                    __syncthreads();
+            // [phase: diag tile inverses]
+            // inverses of the unit-lower diagonal tiles (thread 8 J + c: column c of tile J), so that a block step of the
+            // triangular solves is an 8-term dot product instead of 8 dependent steps
+            for (int i = tid; i < n; i += NT) {
+                const int J = i >> 3, c = i & 7;
+                const double* Lt = sm.tile(J, J);
+                double x[8];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    double acc = (r == c) ? 1.0 : 0.0;
+#pragma unroll
+                    for (int j = 0; j < r; ++j) acc = fma(-Lt[r * 8 + j], x[j], acc);
+                    x[r] = acc;
+                    sm.Dinv[J * 64 + r * 8 + c] = acc;             // zero above the diagonal by construction
                 }
+            }
+            __syncthreads();
+            // [phase: solves]
+            // L D L' x = vec, in place, one block barrier per tile column
+            auto solve = [&]() {
+                for (int J = 0; J < sm.nt; ++J) {                  // forward: L z = r
+                    const int tj = (8 * J) % NT;                   // first of the 8 threads that own tile J's unknowns
+                    if (wid == (tj >> 5)) {
+                        const bool mine = (tid >> 3) == (tj >> 3);
+                        double z = 0.0;
+                        if (mine) {
+                            const double* Li = sm.Dinv + J * 64 + (tid & 7) * 8;
+                            const double* v = sm.vec + 8 * J;
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) z = fma(Li[c], v[c], z);
+                        }
+                        __syncwarp();
+                        if (mine) sm.vec[8 * J + (tid & 7)] = z;
+                    }
+                    __syncthreads();
+                    for (int i = tid; i < n; i += NT) {
+                        if ((i >> 3) <= J) continue;
+                        const double* row = sm.tile(i >> 3, J) + (i & 7) * 8;
+                        const double* v = sm.vec + 8 * J;
+                        double acc = sm.vec[i];
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) acc = fma(-row[c], v[c], acc);
+                        sm.vec[i] = acc;
+                    }
+                    __syncwarp();
+                }
+                __syncthreads();
                 for (int i = tid; i < n; i += NT) sm.vec[i] *= sm.dinv[i];
                 __syncthreads();
-                for (int k = n - 1; k >= 1; --k) {                 // backward: row k of L is contiguous
-                    const double xk = sm.vec[k];
-                    const double* row = sm.M + idx(k, 0);
-                    for (int j = tid; j < k; j += NT) sm.vec[j] = fma(-row[j], xk, sm.vec[j]);
+                for (int J = sm.nt - 1; J >= 0; --J) {             // backward: L' x = y
+                    const int tj = (8 * J) % NT;
+                    if (wid == (tj >> 5)) {
+                        const bool mine = (tid >> 3) == (tj >> 3);
+                        double z = 0.0;
+                        if (mine) {
+                            const double* Lc = sm.Dinv + J * 64 + (tid & 7);
+                            const double* v = sm.vec + 8 * J;
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) z = fma(Lc[c * 8], v[c], z);
+                        }
+                        __syncwarp();
+                        if (mine) sm.vec[8 * J + (tid & 7)] = z;
+                    }
                     __syncthreads();
+                    for (int i = tid; i < 8 * J; i += NT) {
+                        const double* col = sm.tile(J, i >> 3) + (i & 7);
+                        const double* v = sm.vec + 8 * J;
+                        double acc = sm.vec[i];
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) acc = fma(-col[c * 8], v[c], acc);
+                        sm.vec[i] = acc;
+                    }
+                    __syncwarp();
                 }
+                __syncthreads();
             };
 
+            // [phase: predictor]
             // ---- predictor ---------------------------------------------------------------------------------------
             double dsa[8], dla[8];
             double sigma_mu;
@@ -569,6 +727,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                 const double r = mu_aff / mu;
                 sigma_mu = r * r * r * mu;
             }
+            // [phase: corrector + step]
             // ---- corrector ---------------------------------------------------------------------------------------
             {
                 double rc[8], y[8], ya, yd;
@@ -609,12 +768,18 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             }
             ++it;
         }
+        // [phase: epilogue]
         iters = it;
         if (converged) status = MPCB_ST_OPTIMAL;
         else if (feasible0 && best_m < 100.0) { status = best_m < 1.0 ? MPCB_ST_OPTIMAL : MPCB_ST_INACCURATE; a = best_a; d = best_d; }
         else { status = MPCB_ST_FAILED; solved = false; break; }
         solved = true;
         oa = a; od = d;
+        if (p.lam_ws && act) {
+            double* __restrict__ lw = p.lam_ws + (size_t)b * 8 * T;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) lw[c * T + tid] = lam[c];
+        }
         {
             double xs, ys, vs, phs;
             predict(a, d, xs, ys, vs, phs);

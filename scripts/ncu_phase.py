@@ -1,13 +1,14 @@
 import re,csv,sys
 from collections import defaultdict
 sass, prof = sys.argv[1], sys.argv[2]
+SRC = sys.argv[4] if len(sys.argv) > 4 else 'mpcb_step.cuh'
 cur=None; inst_line=[]; ops=[]
 for ln in open(sass):
     if '//## File' in ln:
         ms=re.findall(r'File "([^"]+)", line (\d+)',ln)
         pick=None
         for f,l in ms:
-            if f.endswith('mpcb_step.cuh'): pick=int(l)
+            if f.endswith(SRC): pick=int(l)
         cur=pick if pick else cur; continue
     m=re.match(r'\s+/\*[0-9a-f]{4,}\*/\s+(@!?U?P\d\s+)?([A-Z0-9_.]+)',ln)
     if m: inst_line.append(cur); ops.append(m.group(2).split('.')[0])
@@ -16,7 +17,7 @@ hdr=rows[1]; ix={h:i for i,h in enumerate(hdr)}
 data=[r for r in rows[2:] if len(r)==len(hdr) and r[0]!='Address']
 if len(data)!=len(inst_line) and len(data)%len(inst_line)==0: data=data[:len(inst_line)]   # several captures of the same kernel: first one
 assert len(data)==len(inst_line),(len(data),len(inst_line))
-src=open('/root/repo/mpc_for_av_at_intersection_b200/csrc/mpcb_step.cuh').read().split('\n')
+src=open('/root/repo/mpc_for_av_at_intersection_b200/csrc/'+SRC).read().split('\n')
 marks=[(1,'file head')]
 for i,l in enumerate(src):
     m=re.search(r'// \[phase: (.+?)\]',l)
