@@ -83,6 +83,11 @@ typedef struct mpcb_config {
     /* controller variant main/lib/mpc_with_speed.py: speed reference xref[2,t] = cv[idx_t] (:104) with cv = ref_speed
      * (its MAX_SPEED = 25/3.6, :36,280) and 0 from the per-problem cutoff index on (:281-282).  0 = main/lib/mpc.py */
     double ref_speed;
+    /* controller variant main/lib/mpc_jerk.py: NX = 5, the fifth state integrates the acceleration input from a FREE initial
+     * value and feeds the speed (`A[2,4] = dt`, `A[4,4] = 1`, `B[4,0] = dt`, :61-86), plus a penalty on its increments
+     * (jerk_penalty_weight, :30,190).  jerk_model = 1 selects the jerk kernel (T = 10, 13, 20); 0 = main/lib/mpc.py */
+    int jerk_model;
+    double jerk_weight;
 } mpcb_config;
 
 typedef struct mpcb_handle mpcb_handle;
@@ -209,6 +214,13 @@ int mpcb_session_set_speed_cutoff_host(mpcb_handle* h, const int* cutoff_idx_hos
  * step kernel on the resident session, copies di_ai[B,2] (steer, accel) and status[B] (may be NULL)
  * out.  Synchronous. */
 int mpcb_session_step_host(mpcb_handle* h, const double* state_host, double* di_ai_host, int* status_host);
+/* replaces: `di, ai = mpc.step(state)` TOGETHER with the reads a scenario script does afterwards (mpc.ox, mpc.oy, mpc.xref,
+ * mpc.target_ind, mpc.oa ..., main/lib/mpc.py:289-292, main/scenarios/mpc_intersection.py:297-302) in one synchronisation:
+ * optional target_ind / warm overrides in (NULL = keep the session's), state in, the step, every non-NULL output out.
+ * This is what the B = 1 facade compat.mpc.MPC.step calls.  Synchronous. */
+int mpcb_session_step_all_host(mpcb_handle* h, const double* state_host, const int* target_ind_host, const int* warm_host,
+                               double* di_ai_host, int* status_host, int* target_ind_out, int* iters_out, double* oa_out,
+                               double* od_out, double* traj_out, double* xref_out);
 /* same step on the state already resident in MPCB_F_STATE; asynchronous on `stream`, capturable */
 int mpcb_session_step_dev(mpcb_handle* h, void* stream);
 /* replaces: the loop body of main/scenarios/mpc_intersection.py:95-159 without obstacles, nsteps

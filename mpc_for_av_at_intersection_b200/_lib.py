@@ -30,6 +30,7 @@ class mpcb_config(C.Structure):
         ("car_width", C.c_double), ("car_length", C.c_double), ("coupling_horizon", C.c_double),
         ("frame_window", C.c_int),
         ("ref_speed", C.c_double),
+        ("jerk_model", C.c_int), ("jerk_weight", C.c_double),
     ]
 
 
@@ -43,7 +44,7 @@ EXPORTS = [
     "mpcb_coupling", "mpcb_coupling_host", "mpcb_session_multi_agent_dev",
     "mpcb_session_set_scripted_host", "mpcb_session_scripted_loop_dev",
     "mpcb_session_set_weights_host", "mpcb_session_set_speed_cutoff_host",
-    "mpcb_plan_routes_host", "mpcb_plan_last_error", "mpcb_step_static",
+    "mpcb_plan_routes_host", "mpcb_plan_last_error", "mpcb_step_static", "mpcb_session_step_all_host",
 ]
 
 F_STATE, F_OA, F_OD, F_TRAJ, F_XREF, F_DI_AI, F_XDEV, F_TARGET, F_WARM, F_STATUS, F_ITERS, F_DONE, F_NCOURSE, \
@@ -113,6 +114,8 @@ def lib():
     L.mpcb_session_set_ncourse_host.restype = C.c_int
     L.mpcb_session_step_host.argtypes = [vp, vp, vp, vp]
     L.mpcb_session_step_host.restype = C.c_int
+    L.mpcb_session_step_all_host.argtypes = [vp] * 12
+    L.mpcb_session_step_all_host.restype = C.c_int
     L.mpcb_session_step_dev.argtypes = [vp, vp]
     L.mpcb_session_step_dev.restype = C.c_int
     L.mpcb_session_closed_loop_dev.argtypes = [vp, C.c_int, vp, C.c_int, vp]

@@ -140,19 +140,18 @@ class MPC:
     def step(self, state):
         ses = self._ses
         st = np.array([[state.x, state.y, state.yaw, state.v]], dtype=np.float64)
-        ses.store("target_ind", [self.target_ind])       # callers may set mpc.target_ind directly
-        if self.oa is None or self.odelta is None:
-            ses.store("warm", [0])
-        ses.step(st)
-        status = int(ses.status[0])
+        # one call, one synchronisation: target_ind in (callers may set mpc.target_ind directly), `oa is None` as the warm
+        # flag, the step, and every attribute the reference's callers read afterwards out
+        out = ses.step_all(st, target_ind=[self.target_ind], warm=[0] if (self.oa is None or self.odelta is None) else None)
+        status = int(out["status"][0])
         if status == 3:                                  # main/lib/trajectories.py:120
             raise Exception("something wrong")
-        self.target_ind = int(ses.fetch("target_ind")[0])
-        self.xref = ses.fetch("xref")[0]
+        self.target_ind = int(out["target_ind"][0])
+        self.xref = out["xref"][0]
         if status <= 1:
-            self.oa = ses.fetch("oa")[0]
-            self.odelta = ses.fetch("odelta")[0]
-            traj = ses.fetch("traj")[0]
+            self.oa = out["oa"][0]
+            self.odelta = out["odelta"][0]
+            traj = out["traj"][0]
             self.ox, self.oy, self.ov, self.oyaw = traj[0], traj[1], traj[2], traj[3]
             self.di, self.ai = float(self.odelta[0]), float(self.oa[0])
         else:
@@ -160,7 +159,7 @@ class MPC:
             self.oa = self.odelta = self.ox = self.oy = self.oyaw = self.ov = None
             self.ai = self._cfg.MAX_DECEL                             # mpc.py:294-297: emergency braking, di kept
         self.status = status
-        self.iters = int(ses.fetch("iters")[0])
+        self.iters = int(out["iters"][0])
         return self.di, self.ai
 
     def get_current_xref_deviation(self):

@@ -43,6 +43,9 @@ class MpcConfig:
     frame_window: int = 20
     # variant main/lib/mpc_with_speed.py: speed reference cv (its MAX_SPEED = 25/3.6); 0 = main/lib/mpc.py
     ref_speed: float = 0.0
+    # variant main/lib/mpc_jerk.py (NX = 5: acceleration integrated into a fifth state that feeds the speed, jerk penalty)
+    jerk_model: bool = False
+    jerk_weight: float = 1.0
 
     @staticmethod
     def from_json(path=None, **overrides):
@@ -66,6 +69,14 @@ class MpcConfig:
                  MAX_DSTEER=30.0, MAX_ACCEL=2.0, MAX_DECEL=-5.0, ref_speed=25 / 3.6)
         return MpcConfig.from_dict({**d, **overrides})
 
+    @staticmethod
+    def jerk(**overrides):
+        """The constants main/lib/mpc_jerk.py:16-39,167-171 hard-codes instead of reading the JSON, and its NX = 5 model."""
+        d = dict(NX=5, T=13, w_perp=10.0, w_para=1.0, R=[0.01, 0.01], Rd=[0.3, 1.0], Q_v_yaw=[0.0, 0.5],
+                 Qf=[1.0, 1.0, 0.0, 0.5], GOAL_DIS=1.5, STOP_SPEED=0.5 / 3.6, MAX_TIME=13.0, MAX_ITER=1, DU_TH=0.1,
+                 MAX_DSTEER=30.0, MAX_ACCEL=2.0, MAX_DECEL=-5.0, jerk_model=True, jerk_weight=1.0)
+        return MpcConfig.from_dict({**d, **overrides})
+
     WEIGHT_KEYS = ("w_perp", "w_para", "R", "Rd", "Q_v_yaw", "Qf")
 
     def weight_row(self, **overrides):
@@ -77,8 +88,8 @@ class MpcConfig:
     def to_c(self):
         c = _lib.mpcb_config()
         _lib.lib().mpcb_default_config(c)
-        if self.NX != 4 or self.NU != 2:
-            raise ValueError("only NX=4, NU=2 (main/lib/mpc.py) is supported")
+        if self.NU != 2 or self.NX != (5 if self.jerk_model else 4):
+            raise ValueError("supported models: NX=4, NU=2 (main/lib/mpc.py) and NX=5 with jerk_model (main/lib/mpc_jerk.py)")
         c.T, c.max_iter = int(self.T), int(self.MAX_ITER)
         c.w_perp, c.w_para = float(self.w_perp), float(self.w_para)
         for i in range(2):
@@ -93,4 +104,5 @@ class MpcConfig:
         c.car_width, c.car_length = float(self.car_width), float(self.car_length)
         c.coupling_horizon, c.frame_window = float(self.coupling_horizon), int(self.frame_window)
         c.ref_speed = float(self.ref_speed)
+        c.jerk_model, c.jerk_weight = int(bool(self.jerk_model)), float(self.jerk_weight)
         return c

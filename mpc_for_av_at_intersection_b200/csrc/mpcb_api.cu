@@ -63,6 +63,7 @@ struct mpcb_handle {
         bool hasL = false, has_script = false, has_pw = false, has_vcut = false;
         std::vector<int> route_host;                   // host copy of the routes: the host-array entry points validate indices against it
         size_t pin_state = 0, pin_diai = 0, pin_status = 0, pin_total = 0;
+        char* pin_all = nullptr; size_t pin_all_bytes = 0;     // staging of mpcb_session_step_all_host (allocated on first use)
     } ses;
 };
 
@@ -173,12 +174,13 @@ int launch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st);
 
 // long horizons (mpcb_step_long.cuh): one CTA per problem, system matrix in shared memory
-template <int NT, int MINB = 1>
+template <int NT, int MINB = 1, bool JERK = false>
 int launch_step_long_nt(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     const int T = h->cfg.T;
-    if (T + 1 > NT || T % 4 != 0) { h->err = "mpcb: the CTA-per-problem kernel needs T + 1 <= threads and T a multiple of 4 (8x8 tiles)"; return MPCB_EINVAL; }
-    const size_t smem = mpcb::LongSmem::bytes(T, NT);
-    auto kern = mpcb::mpc_step_long_kernel<NT, MINB>;
+    if (!JERK && (T + 1 > NT || T % 4 != 0)) { h->err = "mpcb: the CTA-per-problem kernel needs T + 1 <= threads and T a multiple of 4 (8x8 tiles)"; return MPCB_EINVAL; }
+    if (JERK && (int)mpcb::LongSmem::unknowns(T, true) > NT) { h->err = "mpcb: the jerk kernel needs 2 T + 1 <= 64 unknowns"; return MPCB_EINVAL; }
+    const size_t smem = mpcb::LongSmem::bytes(T, NT, JERK);
+    auto kern = mpcb::mpc_step_long_kernel<NT, MINB, JERK>;
     static thread_local int configured_dev = -1;
     static thread_local size_t configured_smem = 0;
     if (configured_dev != h->device || configured_smem < smem) {
@@ -230,7 +232,7 @@ StepParams make_params(const mpcb_handle* h) {
     p.dt = c.dt; p.wheelbase = c.wheelbase; p.max_iter = c.max_iter; p.ipm_max_iter = c.ipm_max_iter;
     p.tol_mu = c.ipm_tol_mu; p.tol_p = c.ipm_tol_p; p.tol_d = c.ipm_tol_d;
     p.goal_dis = c.goal_dis; p.stop_speed = c.stop_speed;
-    p.ref_speed = c.ref_speed;
+    p.ref_speed = c.ref_speed; p.jerk_weight = c.jerk_weight;
     return p;
 }
 
@@ -253,6 +255,7 @@ void mpcb_default_config(mpcb_config* c) {
     c->ipm_max_iter = 100; c->ipm_tol_mu = 1e-12; c->ipm_tol_p = 1e-10; c->ipm_tol_d = 1e-9;
     c->car_width = 2.0; c->car_length = 2.86 + 0.64;      // BicycleModelDimensions (car_dimensions.py:82-90)
     c->coupling_horizon = 7.0; c->frame_window = 20;      // mpc_intersection.py:81-82
+    c->jerk_model = 0; c->jerk_weight = 1.0;              // mpc_jerk.py:30
 }
 
 int mpcb_device_count(void) {
@@ -275,6 +278,7 @@ int mpcb_create(const mpcb_config* cfg, int max_batch, int device, mpcb_handle**
     for (int t : kHorizons) okT = okT || (t == cfg->T);
     if (!okT) { g_create_error = "mpcb_create: horizon T=" + std::to_string(cfg->T) + " has no kernel in this build"; return MPCB_EINVAL; }
     if (cfg->max_iter < 1 || cfg->dt <= 0) { g_create_error = "mpcb_create: bad config"; return MPCB_EINVAL; }
+    if (cfg->jerk_model && cfg->T > 28) { g_create_error = "mpcb_create: the jerk model (main/lib/mpc_jerk.py) is built for T <= 28"; return MPCB_EINVAL; }
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) {
         g_create_error = "mpcb_create: no usable CUDA device (this library has no CPU fallback)";
@@ -303,6 +307,7 @@ void mpcb_destroy(mpcb_handle* h) {
     if (h->ramp_dev) cudaFree(h->ramp_dev);
     if (h->ses.slab) cudaFree(h->ses.slab);
     if (h->ses.pin) cudaFreeHost(h->ses.pin);
+    if (h->ses.pin_all) cudaFreeHost(h->ses.pin_all);
     if (h->stage.pinned) cudaFreeHost(h->stage.pinned);
     if (h->stage.dev) cudaFree(h->stage.dev);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -497,6 +502,7 @@ int mpcb_step_host(mpcb_handle* h, int B, const double* state, const int* route,
 namespace {
 
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
+    if (h->cfg.jerk_model) return launch_step_long_nt<64, 4, true>(h, p, st);      // main/lib/mpc_jerk.py
     if (p.pw || p.vcut || p.ref_speed != 0.0) {        // controller variants: their own instantiation
         switch (h->cfg.T) {
             case 10: return launch_step<10, 1, 8, true>(h, p, st);
@@ -701,6 +707,56 @@ int mpcb_session_step_host(mpcb_handle* h, const double* state_host, double* di_
     CUDA_TRY(h, cudaStreamSynchronize(st));
     memcpy(di_ai_host, s.pin + s.pin_diai, 16 * B);
     if (status_host) memcpy(status_host, s.pin + s.pin_status, 4 * B);
+    return MPCB_OK;
+}
+
+// One MPC.step of the resident session with everything a caller of the reference reads afterwards (mpc.py:289-292 and
+// the attribute reads of main/scenarios/mpc_intersection.py:297-302) in ONE synchronisation: inputs staged by asynchronous
+// copies, the kernel, then one asynchronous D2H per requested field into pinned memory and a single stream wait.
+int mpcb_session_step_all_host(mpcb_handle* h, const double* state_host, const int* target_ind_host, const int* warm_host,
+                               double* di_ai_host, int* status_host, int* target_ind_out, int* iters_out, double* oa_out,
+                               double* od_out, double* traj_out, double* xref_out) {
+    if (!h || !state_host || !di_ai_host || h->ses.B <= 0) { if (h) h->err = "mpcb_session_step_all_host: bad arguments / no session"; return MPCB_EINVAL; }
+    auto& s = h->ses;
+    const size_t B = (size_t)s.B, T = (size_t)h->cfg.T;
+    if (target_ind_host)
+        for (size_t b = 0; b < B; ++b)
+            if (target_ind_host[b] < 0) { h->err = "mpcb_session_step_all_host: target_ind must be >= 0"; return MPCB_EINVAL; }
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    if (h->last_stream_set) CUDA_TRY(h, cudaStreamSynchronize(h->last_stream));
+    size_t o = 0;
+    auto put = [&](size_t bytes) { size_t at = o; o = align256(o + bytes); return at; };
+    const size_t p_state = put(32 * B), p_tgt = put(4 * B), p_warm = put(4 * B), p_diai = put(16 * B), p_status = put(4 * B),
+                 p_iters = put(4 * B), p_oa = put(8 * T * B), p_od = put(8 * T * B), p_traj = put(32 * (T + 1) * B), p_xref = put(32 * (T + 1) * B);
+    if (s.pin_all_bytes < o) {
+        if (s.pin_all) cudaFreeHost(s.pin_all);
+        s.pin_all = nullptr; s.pin_all_bytes = 0;
+        CUDA_TRY(h, cudaMallocHost(&s.pin_all, o));
+        s.pin_all_bytes = o;
+    }
+    char* pin = s.pin_all;
+    cudaStream_t st = h->own_stream;
+    memcpy(pin + p_state, state_host, 32 * B);
+    CUDA_TRY(h, cudaMemcpyAsync(s.state, pin + p_state, 32 * B, cudaMemcpyHostToDevice, st));
+    if (target_ind_host) { memcpy(pin + p_tgt, target_ind_host, 4 * B); CUDA_TRY(h, cudaMemcpyAsync(s.target, pin + p_tgt, 4 * B, cudaMemcpyHostToDevice, st)); }
+    if (warm_host) { memcpy(pin + p_warm, warm_host, 4 * B); CUDA_TRY(h, cudaMemcpyAsync(s.warm, pin + p_warm, 4 * B, cudaMemcpyHostToDevice, st)); }
+    int rc = dispatch_step(h, session_params(h), st);
+    if (rc != MPCB_OK) return rc;
+    auto down = [&](void* want, size_t at, const void* dev, size_t bytes) {
+        return want ? cudaMemcpyAsync(pin + at, dev, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
+    };
+    CUDA_TRY(h, down(di_ai_host, p_diai, s.di_ai, 16 * B));
+    CUDA_TRY(h, down(status_host, p_status, s.status, 4 * B));
+    CUDA_TRY(h, down(target_ind_out, p_tgt, s.target, 4 * B));
+    CUDA_TRY(h, down(iters_out, p_iters, s.iters, 4 * B));
+    CUDA_TRY(h, down(oa_out, p_oa, s.oa, 8 * T * B));
+    CUDA_TRY(h, down(od_out, p_od, s.od, 8 * T * B));
+    CUDA_TRY(h, down(traj_out, p_traj, s.traj, 32 * (T + 1) * B));
+    CUDA_TRY(h, down(xref_out, p_xref, s.xref, 32 * (T + 1) * B));
+    CUDA_TRY(h, cudaStreamSynchronize(st));
+    auto out = [&](void* want, size_t at, size_t bytes) { if (want) memcpy(want, pin + at, bytes); };
+    out(di_ai_host, p_diai, 16 * B); out(status_host, p_status, 4 * B); out(target_ind_out, p_tgt, 4 * B); out(iters_out, p_iters, 4 * B);
+    out(oa_out, p_oa, 8 * T * B); out(od_out, p_od, 8 * T * B); out(traj_out, p_traj, 32 * (T + 1) * B); out(xref_out, p_xref, 32 * (T + 1) * B);
     return MPCB_OK;
 }
 

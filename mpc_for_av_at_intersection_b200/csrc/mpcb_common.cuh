@@ -41,6 +41,7 @@ struct StepParams {
     const double* pw;        // [B,12] or null: per-problem w_perp w_para R0 R1 Rd0 Rd1 Qv Qyaw Qf0..3 (Qf scaled by T) --
                              //   main/lib/mpc_sensitivity.py:150-158 re-reads its JSON on every solve
     const int* vcut;         // [B] or null: main/lib/mpc_with_speed.py:276-282 cutoff_idx (cv[cutoff_idx:] = 0)
+    double jerk_weight;      // main/lib/mpc_jerk.py:30,190 jerk_penalty_weight (jerk kernels only)
     double ref_speed;        // cv elsewhere (mpc_with_speed.py:36,280: 25/3.6); xref[2,t] = cv[idx_t] (:104)
     // longest-first launch order for the next control step (resident sessions only; all null = launch slot i solves problem i)
     int* lpt_order;          // [B] io: slot -> problem of THIS launch; rewritten by the last warp to finish, sorted by the

@@ -161,14 +161,17 @@ struct LongSmem {
     double* red;      // scratch of the block primitives
     int* redi;
     static constexpr int NTAB = 24;
-    __host__ __device__ static size_t bytes(int T, int NT) {
-        const size_t n = 2 * (size_t)T, nt = n / 8;
-        return (nt * (nt + 1) / 2 * 64 + nt * 64 + 8 * n + 2 * n + (size_t)NTAB * (T + 1) + NT / 32 + 4) * sizeof(double) +
-               (NT / 32 + 4) * sizeof(int);
+    double* scr;      // jerk variant only: 2 (T + 1)^2 scratch of the pull-back through E
+    __host__ __device__ static size_t unknowns(int T, bool jerk) { return jerk ? (size_t)((2 * T + 1 + 7) & ~7) : 2 * (size_t)T; }
+    __host__ __device__ static size_t bytes(int T, int NT, bool jerk = false) {
+        const size_t n = unknowns(T, jerk), nt = n / 8;
+        return (nt * (nt + 1) / 2 * 64 + nt * 64 + 8 * n + 2 * n + (size_t)NTAB * (T + 1) + NT / 32 + 4 +
+                (jerk ? 2 * (size_t)(T + 1) * (T + 1) : 0)) * sizeof(double) + (NT / 32 + 4) * sizeof(int);
     }
-    __device__ __forceinline__ void carve(unsigned char* raw, int T_, int NT) {
-        T = T_; n = 2 * T_; nt = n >> 3;
+    __device__ __forceinline__ void carve(unsigned char* raw, int T_, int NT, bool jerk = false) {
+        T = T_; n = (int)unknowns(T_, jerk); nt = n >> 3;
         double* q = reinterpret_cast<double*>(raw);
+        scr = q; if (jerk) q += 2 * (size_t)(T + 1) * (T + 1);
         M = q; q += (size_t)nt * (nt + 1) / 2 * 64;
         Dinv = q; q += (size_t)nt * 64;
         Lp = q; q += 4 * n;
@@ -189,19 +192,26 @@ enum { LT_OA = 0, LT_TERM, LT_ZX, LT_ZY, LT_WX, LT_WY, LT_BB, LT_HH, LT_GAX, LT_
        LT_DGA, LT_DGC, LT_WVS, LT_DA, LT_DC, LT_WRP, LT_U0, LT_U1, LT_SPARE };
 
 // [phase: kernel head/inputs]
-template <int NT, int MINB = 1>
+// JERK = true: the controller variant main/lib/mpc_jerk.py -- a fifth state z, the integral of the
+// acceleration input with a FREE initial value, feeding the speed (`A[2,4] = dt`, :61-86): v_{t+1} = v_t + dt (a_t + z_t).
+// With e = a + z ("effective" acceleration), z_k = z_0 + dt sum_{j<k} a_j, the tracking cost and the speed bounds are those of
+// the standard model evaluated at e = E [a; z_0]; the kernel pulls gradient, Hessian and speed rows back through E
+// (prefix / suffix sums) and carries z_0 as unknown number 2T (n = 2T + 1, padded to a multiple of 8 with identity rows);
+// the jerk penalty (z_{t+1} - z_t)^2 = dt^2 a_t^2, t <= T - 2 (:190), is a diagonal input cost.  Derivation checked against the
+// goldens recorded from the unmodified module in oracle/condensed_jerk.py.
+template <int NT, int MINB = 1, bool JERK = false>
 __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParams p, const int T) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int b = blockIdx.x;
     if (b >= p.B) return;
     LongSmem sm;
-    sm.carve(smem_raw, T, NT);
+    sm.carve(smem_raw, T, NT, JERK);
     BlockOps<NT> bo(sm.red, sm.redi);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     constexpr int NW = NT / 32;
     const bool act = tid < T;
     const double dt = p.dt;
-    const int n = 2 * T;
+    const int n = sm.n;
 
     if (p.done && p.done[b] != 0) return;
     const double x0 = p.state[4 * b + 0], y0 = p.state[4 * b + 1], yaw0 = p.state[4 * b + 2], v0 = p.state[4 * b + 3];
@@ -354,7 +364,21 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
 
         // [phase: predict/grad/G defs]
         // ---- linear prediction and objective gradient by scans (oracle/condensed_model.py states()/grad()) ----
-        auto predict = [&](double a, double d, double& xs, double& ys, double& vs, double& phs) {
+        // jerk variant: effective acceleration e_t = a_t + z_t, z_t = z0 + dt sum_{j<t} a_j, and the adjoint of that map
+        // (a gradient with respect to e pulled back to (a, z0))
+        auto effective = [&](double a, double z0) {
+            if constexpr (!JERK) return a;
+            else {
+                const double pre = bo.scan_up(a) - a;            // block primitive: every thread takes part
+                return act ? a + z0 + dt * pre : 0.0;
+            }
+        };
+        auto pull_back = [&](double ge, double& ga, double& gz) {
+            if constexpr (!JERK) { ga = ge; gz = 0.0; }
+            else { ga = ge + dt * (bo.scan_dn(ge) - ge); gz = bo.sum(ge); }
+        };
+        auto predict = [&](double a_in, double d, double z0, double& xs, double& ys, double& vs, double& phs) {
+            const double a = effective(a_in, z0);
             const double sa = bo.scan_up(a);
             const double bd_ = bb * d;
             const double sp_ = bo.scan_up(bd_);
@@ -365,9 +389,9 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             xs = x0 + bo.scan_up(c_ * vt - pp * dph);
             ys = y0 + bo.scan_up(s_ * vt + qq * dph);
         };
-        auto gradient = [&](double a, double d, double& ga, double& gd) {
+        auto gradient = [&](double a, double d, double z0, double& ga, double& gd, double& gz) {
             double xs, ys, vs, phs;
-            predict(a, d, xs, ys, vs, phs);
+            predict(a, d, z0, xs, ys, vs, phs);
             const double ex = xs - rx, ey = ys - ry;
             const double lx = 2.0 * (m11 * ex + m12 * ey), ly = 2.0 * (m12 * ex + m22 * ey);
             const double lv = 2.0 * wv * (vs - rv), lp = 2.0 * wp * (phs - rpsi);      // rv = 0: xref[2,:] = 0 (mpc.py:102-105)
@@ -379,18 +403,23 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             const double dp = bo.up1(d), dn = bo.dn1(d);
             const double fa = (tid > 0 ? a - ap : 0.0) - (tid < T - 1 ? an - a : 0.0);
             const double fd = (tid > 0 ? d - dp : 0.0) - (tid < T - 1 ? dn - d : 0.0);
-            ga = act ? dt * pv + 2.0 * ra_w * a + 2.0 * Rd0 * fa : 0.0;
+            double gt;
+            pull_back(act ? dt * pv : 0.0, gt, gz);
+            ga = act ? gt + 2.0 * ra_w * a + 2.0 * Rd0 * fa : 0.0;
+            if constexpr (JERK) ga += (tid < T - 1) ? 2.0 * p.jerk_weight * dt * dt * a : 0.0;     // mpc_jerk.py:190
             gd = act ? bb * pph + 2.0 * rd_w * d + 2.0 * Rd1 * fd : 0.0;
         };
         // structured constraint operator, slots as in mpcb_step.cuh (main/lib/mpc.py:184,187-191)
-        auto G_apply = [&](double a, double d, double (&g)[8]) {
+        auto G_apply = [&](double a, double d, double z0, double (&g)[8]) {
             const double dn = bo.dn1(d);
             const double dd = (tid < T - 1) ? dn - d : 0.0;
-            const double cs2 = dt * bo.scan_up(a);
+            const double cs2 = dt * bo.scan_up(effective(a, z0));
             g[0] = a; g[1] = -a; g[2] = d; g[3] = -d; g[4] = dd; g[5] = -dd; g[6] = cs2; g[7] = -cs2;
         };
-        auto GT_apply = [&](const double (&y)[8], double& ga, double& gd) {
-            ga = y[0] - y[1] + dt * bo.scan_dn(y[6] - y[7]);
+        auto GT_apply = [&](const double (&y)[8], double& ga, double& gd, double& gz) {
+            double gs;
+            pull_back(dt * bo.scan_dn(y[6] - y[7]), gs, gz);
+            ga = y[0] - y[1] + gs;
             const double r = y[4] - y[5];
             gd = y[2] - y[3] - r + bo.up1(r);
         };
@@ -407,16 +436,17 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
         const bool feasible0 = (hh8[6] >= -1e-9) && (hh8[7] >= -1e-9);
 
         double a = act ? oa : 0.0, d = act ? od : 0.0;
+        double z0 = 0.0;                                 // jerk variant: free initial value of the fifth state (every thread holds it)
         double gscale;
         {
-            double g0a, g0d;
-            gradient(0.0, 0.0, g0a, g0d);
-            gscale = 1.0 + bo.max(fmax(fabs(g0a), fabs(g0d)));
+            double g0a, g0d, g0z;
+            gradient(0.0, 0.0, 0.0, g0a, g0d, g0z);
+            gscale = 1.0 + bo.max(fmax(fmax(fabs(g0a), fabs(g0d)), fabs(g0z)));
         }
         double s[8], lam[8];      // centred, gradient-scaled start: see mpcb_step.cuh
         {
             double g[8];
-            G_apply(a, d, g);
+            G_apply(a, d, z0, g);
             const double mu0 = fmax(10.0, 0.01 * gscale);
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
@@ -438,16 +468,16 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
         int it = 0;
         double mu_prev = 1e300;
         bool eta_safe = false;
-        double best_m = 1e300, best_a = 0.0, best_d = 0.0;      // best iterate so far and its merit, see mpcb_step.cuh
+        double best_m = 1e300, best_a = 0.0, best_d = 0.0, best_z = 0.0;      // best iterate so far and its merit, see mpcb_step.cuh
         // [phase: residuals + tests]
         while (feasible0) {
-            double rda, rdd, rp[8];
+            double rda, rdd, rdz, rp[8];
             {
-                double ga, gd, gta, gtd, g[8];
-                gradient(a, d, ga, gd);
-                GT_apply(lam, gta, gtd);
-                rda = ga + gta; rdd = gd + gtd;
-                G_apply(a, d, g);
+                double ga, gd, gz, gta, gtd, gtz, g[8];
+                gradient(a, d, z0, ga, gd, gz);
+                GT_apply(lam, gta, gtd, gtz);
+                rda = ga + gta; rdd = gd + gtd; rdz = gz + gtz;
+                G_apply(a, d, z0, g);
                 double sl = 0.0, rpm = 0.0;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
@@ -456,7 +486,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                     rpm = fmax(rpm, fabs(rp[c]));
                 }
                 mu = bo.sum(sl) / m_cnt;
-                res_d = bo.max(fmax(fabs(rda), fabs(rdd)));
+                res_d = bo.max(fmax(fmax(fabs(rda), fabs(rdd)), fabs(rdz)));
                 res_p = bo.max(rpm);
             }
 #ifdef MPCB_TRACE
@@ -467,7 +497,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
 #endif
             {
                 const double m = fmax(fmax(res_d / (1e-8 * gscale), res_p * 1e9), mu * 1e9);
-                if (m < best_m && m < 100.0) { best_m = m; best_a = a; best_d = d; }
+                if (m < best_m && m < 100.0) { best_m = m; best_a = a; best_d = d; best_z = z0; }
             }
             if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) { converged = true; break; }
             if (it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) break;
@@ -487,17 +517,71 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             }
             // affine right-hand side: -r_d + G'(lam - W r_p)
             {
-                double y[8], ya, yd;
+                double y[8], ya, yd, yz;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) y[c] = lam[c] - w[c] * rp[c];
-                GT_apply(y, ya, yd);
+                GT_apply(y, ya, yd, yz);
                 if (act) { sm.vec[tid] = ya - rda; sm.vec[T + tid] = yd - rdd; }
+                if constexpr (JERK) { if (tid >= 2 * T && tid < n) sm.vec[tid] = tid == 2 * T ? yz - rdz : 0.0; }
             }
             __syncthreads();
             // [phase: assemble M]
             // ---- assemble M = H + G'WG tile by tile (unknowns a_0..a_{T-1}, d_0..d_{T-1}; T is a multiple of 4, so a tile
             //      lies inside one of the three blocks): lane l writes elements [l/4][2 (l%4)], [l/4][2 (l%4) + 1] ----------
-            {
+            if constexpr (JERK) {
+                // jerk variant: Hessian in (e, delta) incl. the speed rows' dt^2 L'WL (it acts on e like the tracking cost),
+                // pulled back through e = E [a; z0]: P <- E' P E, B <- B E by running sums (T is small: one thread per row /
+                // column), then scattered with the input terms into the tiles; unknowns [a | delta | z0 | identity padding]
+                const int ld = T + 1;
+                double* P = sm.scr;                                // (T + 1) x (T + 1): rows / columns 0..T-1 = e, T = z0
+                double* Bq = sm.scr + ld * ld;                     // T x (T + 1): steer rows, columns as P
+                const double kA = 2.0 * dt * dt;
+                for (int idx = tid; idx < T * T; idx += NT) {
+                    const int i = idx / T, j = idx - i * T, hi = max(i, j), lo = min(i, j);
+                    P[i * ld + j] = kA * (sm.t(LT_HA)[hi] + sm.t(LT_ZX)[lo] * sm.t(LT_GAX)[hi] + sm.t(LT_ZY)[lo] * sm.t(LT_GAY)[hi]) + sm.t(LT_WVS)[hi];
+                    const double Blo = sm.t(LT_HB)[i] + sm.t(LT_ZX)[j] * sm.t(LT_GCX)[i] + sm.t(LT_ZY)[j] * sm.t(LT_GCY)[i];
+                    const double Bup = sm.t(LT_HH)[j] + sm.t(LT_WX)[i] * sm.t(LT_GAX)[j] + sm.t(LT_WY)[i] * sm.t(LT_GAY)[j];
+                    Bq[i * ld + j] = 2.0 * sm.t(LT_BB)[i] * dt * ((j <= i) ? Blo : Bup);
+                }
+                __syncthreads();
+                if (tid < 2 * T) {                                 // right-multiply by E: row[k] += dt sum_{t>k} row[t], row[T] = sum
+                    double* row = tid < T ? P + tid * ld : Bq + (tid - T) * ld;
+                    double tot = 0.0;
+                    for (int k = T - 1; k >= 0; --k) { const double v = row[k]; row[k] = v + dt * tot; tot += v; }
+                    row[T] = tot;
+                }
+                __syncthreads();
+                if (tid <= T) {                                    // left-multiply P by E': the same down every column
+                    double tot = 0.0;
+                    for (int k = T - 1; k >= 0; --k) { const double v = P[k * ld + tid]; P[k * ld + tid] = v + dt * tot; tot += v; }
+                    P[T * ld + tid] = tot;
+                }
+                __syncthreads();
+                for (int idx = tid; idx < n * n; idx += NT) {
+                    const int i = idx / n, j = idx - i * n;
+                    if (j > (i | 7)) continue;
+                    double x = 0.0;
+                    if (j <= i) {
+                        if (i < T) {                               // a_i, a_j
+                            x = P[i * ld + j];
+                            if (j == i) x += sm.t(LT_DGA)[i] + sm.t(LT_DA)[i] + (i < T - 1 ? 2.0 * p.jerk_weight * dt * dt : 0.0);
+                            if (j == i - 1) x -= 2.0 * Rd0;
+                        } else if (i < 2 * T) {
+                            const int r = i - T;
+                            if (j < T) x = Bq[r * ld + j];         // delta_r, a_j
+                            else {                                 // delta_r, delta_q
+                                const int q = j - T;
+                                x = 2.0 * sm.t(LT_BB)[r] * sm.t(LT_BB)[q] * (sm.t(LT_HC)[r] + sm.t(LT_WX)[q] * sm.t(LT_GCX)[r] + sm.t(LT_WY)[q] * sm.t(LT_GCY)[r]);
+                                if (q == r) x += sm.t(LT_DGC)[r] + sm.t(LT_DC)[r];
+                                if (q == r - 1) x -= 2.0 * Rd1 + sm.t(LT_WRP)[r];
+                            }
+                        } else if (i == 2 * T) {                   // z0 row
+                            x = j < T ? P[T * ld + j] : j < 2 * T ? Bq[(j - T) * ld + T] : P[T * ld + T];
+                        } else x = (j == i) ? 1.0 : 0.0;           // padding
+                    }
+                    sm.tile(i >> 3, j >> 3)[(i & 7) * 8 + (j & 7)] = x;
+                }
+            } else {
                 const double kA = 2.0 * dt * dt;
                 const int er = lane >> 2, ec = (lane & 3) * 2;
                 const int tT = T >> 3;                             // accel tiles per side
@@ -708,8 +792,9 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             {
                 solve();
                 const double da = act ? sm.vec[tid] : 0.0, dd = act ? sm.vec[T + tid] : 0.0;
+                const double dz = JERK ? sm.vec[2 * T] : 0.0;
                 double g[8];
-                G_apply(da, dd, g);
+                G_apply(da, dd, dz, g);
                 double tmax = 0.0;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
@@ -730,19 +815,21 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             // [phase: corrector + step]
             // ---- corrector ---------------------------------------------------------------------------------------
             {
-                double rc[8], y[8], ya, yd;
+                double rc[8], y[8], ya, yd, yz;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     rc[c] = mk[c] ? s[c] * lam[c] + dsa[c] * dla[c] - sigma_mu : 0.0;
                     y[c] = rc[c] * sinv[c] - w[c] * rp[c];
                 }
-                GT_apply(y, ya, yd);
+                GT_apply(y, ya, yd, yz);
                 if (act) { sm.vec[tid] = ya - rda; sm.vec[T + tid] = yd - rdd; }
+                if constexpr (JERK) { if (tid >= 2 * T && tid < n) sm.vec[tid] = tid == 2 * T ? yz - rdz : 0.0; }
                 __syncthreads();
                 solve();
                 const double da = act ? sm.vec[tid] : 0.0, dd = act ? sm.vec[T + tid] : 0.0;
+                const double dz = JERK ? sm.vec[2 * T] : 0.0;
                 double g[8];
-                G_apply(da, dd, g);
+                G_apply(da, dd, dz, g);
                 double tmax = 0.0;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
@@ -762,7 +849,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
 #ifdef MPCB_TRACE
                 if (p.trace && tid == 0 && it < 128) p.trace[((size_t)b * 128 + it) * 8 + 4] = al;
 #endif
-                a += al * da; d += al * dd;
+                a += al * da; d += al * dd; z0 += al * dz;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) { s[c] += al * dsa[c]; lam[c] += al * dla[c]; }
             }
@@ -771,7 +858,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
         // [phase: epilogue]
         iters = it;
         if (converged) status = MPCB_ST_OPTIMAL;
-        else if (feasible0 && best_m < 100.0) { status = best_m < 1.0 ? MPCB_ST_OPTIMAL : MPCB_ST_INACCURATE; a = best_a; d = best_d; }
+        else if (feasible0 && best_m < 100.0) { status = best_m < 1.0 ? MPCB_ST_OPTIMAL : MPCB_ST_INACCURATE; a = best_a; d = best_d; z0 = best_z; }
         else { status = MPCB_ST_FAILED; solved = false; break; }
         solved = true;
         oa = a; od = d;
@@ -782,7 +869,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
         }
         {
             double xs, ys, vs, phs;
-            predict(a, d, xs, ys, vs, phs);
+            predict(a, d, z0, xs, ys, vs, phs);
             sx = bo.up1(xs); sy = bo.up1(ys); sv = bo.up1(vs); sph = bo.up1(phs);    // thread t holds state t
             if (tid == 0) { sx = x0; sy = y0; sv = v0; sph = yaw0; }
         }

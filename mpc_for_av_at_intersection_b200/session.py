@@ -93,6 +93,21 @@ class MpcSession:
                    self._h, "mpcb_session_step_host")
         return self._di_ai[:, 0], self._di_ai[:, 1]
 
+    def step_all(self, state: np.ndarray, target_ind=None, warm=None):
+        """MPC.step plus everything the reference's callers read afterwards, in one synchronisation
+        (mpcb_session_step_all_host).  Returns dict(di_ai, status, target_ind, iters, oa, odelta, traj, xref)."""
+        assert state.dtype == np.float64 and state.shape == (self.B, 4) and state.flags.c_contiguous
+        B, T = self.B, self.cfg.T
+        ti = None if target_ind is None else np.ascontiguousarray(target_ind, dtype=np.int32)
+        wm = None if warm is None else np.ascontiguousarray(warm, dtype=np.int32)
+        out = dict(di_ai=np.empty((B, 2)), status=np.empty(B, np.int32), target_ind=np.empty(B, np.int32), iters=np.empty(B, np.int32),
+                   oa=np.empty((B, T)), odelta=np.empty((B, T)), traj=np.empty((B, 4, T + 1)), xref=np.empty((B, 4, T + 1)))
+        _lib.check(self._lib.mpcb_session_step_all_host(
+            self._h, _p(state), _p(ti), _p(wm), _p(out["di_ai"]), _p(out["status"]), _p(out["target_ind"]), _p(out["iters"]),
+            _p(out["oa"]), _p(out["odelta"]), _p(out["traj"]), _p(out["xref"])), self._h, "mpcb_session_step_all_host")
+        self._di_ai, self._status = out["di_ai"], out["status"]
+        return out
+
     @property
     def status(self):
         return self._status

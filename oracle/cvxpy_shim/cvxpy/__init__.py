@@ -164,6 +164,13 @@ class Quad:
 
     __radd__ = __add__
 
+    def __mul__(self, k):                                   # scalar * expression (main/lib/mpc_jerk.py:190)
+        k = float(k)
+        assert k >= 0.0, "only non-negative scalings keep the objective convex"
+        return Quad([(x, Pm * k) for x, Pm in self.terms], self.const * k)
+
+    __rmul__ = __mul__
+
 
 def quad_form(x, Pm):
     Pm = np.asarray(Pm, float)

@@ -97,3 +97,31 @@ def test_mpc_sensitivity_facade_rereads_its_json(tmp_path, monkeypatch):
             worst = max(worst, abs(delta - g["di"][k]), abs(acc - g["ai"][k]))
     print(f"mpc_sensitivity facade: 3 settings x 25 steps, max|du0| = {worst:.2e}")
     assert worst < 1e-6
+
+
+def test_mpc_jerk_facade_closed_loop():
+    """compat.mpc_jerk.MPC driven like the loop body of main/scenarios/mpc_intersection.py:95-159 (no obstacles) against the
+    loop the unmodified main/lib/mpc_jerk.py recorded: steps to goal identical, controls 1e-6 over the first 40 steps,
+    positions 1e-3 m to the goal."""
+    from mpc_for_av_at_intersection_b200.compat import mpc_jerk as cm
+    from mpc_for_av_at_intersection_b200.compat.simulation import HistorySimulation, State
+    g = golden("variant_jerk.npz")
+    sel = np.flatnonzero((g["kind"] == 0) & (g["loop"] == 0))
+    full = load_routes(False)[int(g["route"][sel[0]])]
+    dl = np.linalg.norm(full[0, :2] - full[1, :2])
+    mpc = cm.MPC(cx=full[:, 0], cy=full[:, 1], cyaw=full[:, 2], dl=dl, dt=0.2, car_dimensions=_car())
+    state = State(x=full[0, 0], y=full[0, 1], yaw=full[0, 2], v=0.0)
+    sim = HistorySimulation(car_dimensions=_car(), sample_time=0.2, initial_state=state)
+    n = 0
+    while not mpc.is_goal(state) and n < 400:
+        delta, acc = mpc.step(state)
+        state = sim.step(a=acc, delta=delta, xref_deviation=mpc.get_current_xref_deviation())
+        n += 1
+    assert n == int(g["loop_len"][0]) == len(sel)
+    h = sim.history
+    got = np.array([h.x, h.y, h.yaw, h.v, h.delta, h.a]).T
+    ref = g["history"][: n + 1]
+    assert got.shape[0] == ref.shape[0]
+    print(f"mpc_jerk facade: {n} steps, max|dpos|={np.abs(got[:, :2] - ref[:, :2]).max():.2e} max|du| first 40={np.abs(got[:41, 4:6] - ref[:41, 4:6]).max():.2e}")
+    assert np.abs(got[:, :2] - ref[:, :2]).max() < 1e-3 and np.abs(got[:41, 4:6] - ref[:41, 4:6]).max() < 1e-6
+    assert cm.NX == 5 and cm.MAX_DECEL == -5

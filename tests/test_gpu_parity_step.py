@@ -179,3 +179,30 @@ def test_mpc_sensitivity_variant_is_one_batch():
     sel = np.arange(len(g40["state"]))
     out = _run_session(cfg40, g40, sel, weights=np.tile(cfg40.weight_row(), (len(sel), 1)))
     _compare(g40, sel, out, 40)
+
+
+def test_mpc_jerk_variant_matches_reference():
+    """main/lib/mpc_jerk.py (NX = 5: the acceleration input is also integrated into a fifth state with a free initial value
+    that feeds the speed, jerk penalty, its hard-coded weights) through the jerk instantiation of the CTA-per-problem
+    kernel: every MPC.step of two closed loops recorded from the unmodified module + 160 randomised steps."""
+    from mpc_for_av_at_intersection_b200 import MpcConfig
+    g = golden("variant_jerk.npz")
+    sel = np.arange(len(g["state"]))
+    out = _run_session(MpcConfig.jerk(), g, sel)
+    T = 13
+    ok = ~g["raised"][sel].astype(bool)
+    assert np.array_equal(out["status"] == 3, ~ok)
+    assert np.array_equal(out["target"][ok], g["target_out"][sel][ok])
+    assert np.array_equal(out["xref"][ok], g["xref"][sel][ok])
+    s = g["solved"][sel].astype(bool)
+    assert np.array_equal((out["status"] <= 1) & ok, s)
+    e_u0 = max(np.abs(out["di_ai"][s, 0] - g["di"][sel][s]).max(), np.abs(out["di_ai"][s, 1] - g["ai"][sel][s]).max())
+    e_u = max(np.abs(out["oa"][s] - g["oa"][sel][s]).max(), np.abs(out["od"][s] - g["od"][sel][s]).max())
+    tr = out["traj"][s]
+    e_x = max(np.abs(tr[:, 0] - g["ox"][sel][s]).max(), np.abs(tr[:, 1] - g["oy"][sel][s]).max(), np.abs(tr[:, 3] - g["oyaw"][sel][s]).max())
+    e_v = np.abs(tr[:, 2] - g["ov"][sel][s]).max()
+    print(f"mpc_jerk: n={len(sel)} solved={s.sum()} max|du0|={e_u0:.2e} max|du|={e_u:.2e} max|dxy,yaw|={e_x:.2e} max|dv|={e_v:.2e} "
+          f"iters mean={out['iters'].mean():.1f} max={out['iters'].max()}")
+    assert e_u0 < 1e-6 and e_u < 2e-4 and e_x < 1e-5 and e_v < 2e-4
+    f = ~s & ok
+    assert np.all(out["di_ai"][f, 1] == -5.0)                 # its own MAX_DECEL (mpc_jerk.py:39)

@@ -135,3 +135,33 @@ def test_oracle_matches_reference_mpc_sensitivity(routes_smooth):
         cfgd = {"T": 13, "w_perp": w[0], "w_para": w[1], "R": w[2:4], "Rd": w[4:6], "Q_v_yaw": w[6:8], "Qf": w[8:12]}
         worst = max(worst, _check_variant(_replay_variant(g, k, routes_smooth, cfgd), g, k))
     assert worst < 1e-7, worst
+
+
+def test_condensed_jerk_model_matches_reference_golden():
+    """oracle/condensed_jerk.py (the math of the CUDA jerk kernel: standard condensed model at the effective acceleration
+    e = E [a; z0], pulled back through E) against steps recorded from the unmodified main/lib/mpc_jerk.py."""
+    import condensed_jerk as cj
+    g = golden("variant_jerk.npz")
+    routes = load_routes(True)
+    T = 13
+    cfg = cj.jerk_cfg(T)
+    worst, n = 0.0, 0
+    for i in range(0, len(g["state"]), 9):
+        if g["raised"][i] or not g["solved"][i]:
+            continue
+        r = int(g["route"][i])
+        full = routes[r]
+        dl = float(np.linalg.norm(full[0, :2] - full[1, :2]))
+        full = full[: int(g["ncourse"][i])]
+        x, y, yaw, v = g["state"][i]
+        warm = bool(g["has_warm"][i])
+        oa = np.nan_to_num(g["oa_in"][i]) if warm else np.zeros(T)
+        od = np.nan_to_num(g["od_in"][i]) if warm else np.zeros(T)
+        xref, tind, idx, re = mo.calc_ref_trajectory(x, y, v, full[:, 0], full[:, 1], full[:, 2], dl, 0.2, int(g["target_in"][i]), T, None, None)
+        assert tind == int(g["target_out"][i])
+        xbar = mo.predict_motion([x, y, v, yaw], list(oa), list(od), 2.86, 0.2, T)
+        sol = cj.CondensedJerk(xref, xbar, [x, y, v, yaw], re, cfg, 2.86, 0.2).solve()
+        worst = max(worst, np.abs(sol["oa"] - g["oa"][i]).max(), np.abs(sol["od"] - g["od"][i]).max(),
+                    np.abs(sol["ov"] - g["ov"][i]).max(), np.abs(sol["ox"] - g["ox"][i]).max())
+        n += 1
+    assert n > 30 and worst < 1e-8, (n, worst)
