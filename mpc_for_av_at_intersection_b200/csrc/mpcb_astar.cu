@@ -12,8 +12,10 @@
 // oracle/astar_oracle.py restates -- the reference itself multiplies through OpenBLAS, whose rounding is machine dependent.
 //
 // Data structures per search (global memory, sized by the caller):
-//   open list   unsorted arrays; a pop is a warp-wide arg-min over the alive entries by the reference's tuple order
-//               (g+h, g, node, predecessor); the searches of the reference's scenarios hold 10^2..10^4 entries
+//   open list   unsorted arrays in blocks of 256 entries with one running minimum of g+h per block; a pop is a warp-wide
+//               arg-min by the reference's tuple order (g+h, g, node, predecessor) over the blocks whose minimum equals the
+//               global one (almost always a single block), so its cost is n_open / 256 block minima + 256 entries instead
+//               of n_open entries: the 10^4-expansion searches (10^5 entries) no longer set the launch time
 //   closed set  arrays + an open-addressing hash table probed 32 slots at a time (exact float equality, like the dict)
 #include <cuda_runtime.h>
 #include <math.h>
@@ -30,6 +32,7 @@
 #define AS_MAX_HP 8
 #define AS_MAX_MP 16
 #define AS_MAX_CC 16
+#define AS_OB 256                 /* open-list block: entries per running minimum */
 
 namespace {
 
@@ -47,6 +50,7 @@ struct AstarParams {
     // workspace
     double *o_gh, *o_g, *o_x, *o_y, *o_t;                 // [B][max_open]
     int *o_pred, *o_mp;
+    double* o_bmin;                                       // [B][max_open / AS_OB + 1] min g+h of the alive entries of a block
     double *c_x, *c_y, *c_t, *c_g;                        // [B][max_closed]
     int *c_pred, *c_mp;
     int* hash;                                            // [B][hash_cap], -1 = empty
@@ -115,6 +119,7 @@ struct Search {
     int lane;
     double *o_gh, *o_g, *o_x, *o_y, *o_t, *c_x, *c_y, *c_t, *c_g;
     int *o_pred, *o_mp, *c_pred, *c_mp, *hash;
+    double* o_bmin;
     double sx, sy, st;                                   // start node (the predecessor of the first entry is itself)
 
     __device__ void pred_xyz(int e, double& x, double& y, double& t) const {
@@ -135,22 +140,42 @@ struct Search {
         if (at != bt) return at < bt;
         return a < b;                                     // identical tuples: any order gives the same search
     }
-    // heappop: the alive entry that is smallest in the reference's tuple order, or -1
+    // heappop: the alive entry that is smallest in the reference's tuple order, or -1.  Two levels: the global minimum of
+    // g+h from the block minima, then the full tuple comparison inside the block(s) that attain it.
     __device__ int pop(int n_open) const {
+        const int nblk = (n_open + AS_OB - 1) / AS_OB;
+        double gmin = inf_d();
+        for (int k = lane; k < nblk; k += 32) gmin = fmin(gmin, o_bmin[k]);
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) gmin = fmin(gmin, __shfl_xor_sync(AS_FULL, gmin, d));
+        if (!(gmin < inf_d())) return -1;
         int best = -1;
-        double bgh = inf_d();
-        for (int i = lane; i < n_open; i += 32) {
-            const double gh = o_gh[i];
-            if (gh < bgh) { best = i; bgh = gh; }
-            else if (gh == bgh && best >= 0 && less_tail(i, best)) best = i;
+        for (int k0 = 0; k0 < nblk; k0 += 32) {
+            const int k = k0 + lane;
+            unsigned cand = __ballot_sync(AS_FULL, k < nblk && o_bmin[k] == gmin);
+            while (cand) {
+                const int blk = k0 + __ffs(cand) - 1;
+                cand &= cand - 1;
+                const int hi = min(n_open, (blk + 1) * AS_OB);
+                for (int i = blk * AS_OB + lane; i < hi; i += 32)
+                    if (o_gh[i] == gmin && (best < 0 || less_tail(i, best))) best = i;
+            }
         }
 #pragma unroll
         for (int d = 16; d >= 1; d >>= 1) {
-            const double ogh = __shfl_xor_sync(AS_FULL, bgh, d);
             const int oi = __shfl_xor_sync(AS_FULL, best, d);
-            if (oi >= 0 && (best < 0 || ogh < bgh || (ogh == bgh && less_tail(oi, best)))) { best = oi; bgh = ogh; }
+            if (oi >= 0 && (best < 0 || less_tail(oi, best))) best = oi;
         }
         return best;
+    }
+    // entry e left the queue: its block's running minimum is recomputed from the entries that are still alive
+    __device__ void refresh_block(int e, int n_open) const {
+        const int blk = e / AS_OB, hi = min(n_open, (blk + 1) * AS_OB);
+        double m = inf_d();
+        for (int i = blk * AS_OB + lane; i < hi; i += 32) m = fmin(m, o_gh[i]);
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) m = fmin(m, __shfl_xor_sync(AS_FULL, m, d));
+        if (lane == 0) o_bmin[blk] = m;
     }
     // `node in pred_dict`: closed index or -1; *slot receives where an insertion would go
     __device__ int lookup(double x, double y, double t, int* slot) const {
@@ -196,10 +221,12 @@ __global__ void __launch_bounds__(32) astar_kernel(const AstarParams p) {
              p.c_g + (size_t)b * p.max_closed,
              p.o_pred + (size_t)b * p.max_open, p.o_mp + (size_t)b * p.max_open,
              p.c_pred + (size_t)b * p.max_closed, p.c_mp + (size_t)b * p.max_closed, p.hash + (size_t)b * p.hash_cap,
+             p.o_bmin + (size_t)b * (p.max_open / AS_OB + 1),
              p.start[3 * b], p.start[3 * b + 1], p.start[3 * b + 2]};
     for (int i = lane; i < p.hash_cap; i += 32) S.hash[i] = -1;
     if (lane == 0) {                                      // q = [(0, 0, start, start)]   (a_star.py:34)
         S.o_gh[0] = 0.0; S.o_g[0] = 0.0; S.o_x[0] = S.sx; S.o_y[0] = S.sy; S.o_t[0] = S.st; S.o_pred[0] = -1; S.o_mp[0] = -1;
+        S.o_bmin[0] = 0.0;
     }
     __syncwarp();
     int n_open = 1, n_closed = 0, n_expanded = 0, status = MPCB_PLAN_NO_SOLUTION, goal_ci = -1;
@@ -212,6 +239,8 @@ __global__ void __launch_bounds__(32) astar_kernel(const AstarParams p) {
         const int pred = S.o_pred[e], mp_in = S.o_mp[e];
         __syncwarp();
         if (lane == 0) S.o_gh[e] = inf_d();
+        __syncwarp();
+        S.refresh_block(e, n_open);
         int slot;
         int ci = S.lookup(x, y, th, &slot);
         if (ci >= 0 && g >= S.c_g[ci]) { __syncwarp(); continue; }      // seen before, not better   (a_star.py:45-49)
@@ -273,8 +302,11 @@ __global__ void __launch_bounds__(32) astar_kernel(const AstarParams p) {
                 const double ad = fabs(__dsub_rn(nt, gth));
                 const double dth = fmin(ad, __dsub_rn(ad, allowed / 2));
                 const double h = __dadd_rn(dxy, __dmul_rn(2.7, dth));      // :71-86
-                S.o_gh[n_open] = __dadd_rn(ng, h); S.o_g[n_open] = ng; S.o_x[n_open] = nx; S.o_y[n_open] = ny; S.o_t[n_open] = nt;
+                const double gh = __dadd_rn(ng, h);
+                S.o_gh[n_open] = gh; S.o_g[n_open] = ng; S.o_x[n_open] = nx; S.o_y[n_open] = ny; S.o_t[n_open] = nt;
                 S.o_pred[n_open] = ci; S.o_mp[n_open] = m;
+                const int blk = n_open / AS_OB;
+                S.o_bmin[blk] = (n_open % AS_OB == 0) ? gh : fmin(S.o_bmin[blk], gh);
             }
             ++n_open;
         }
@@ -372,7 +404,7 @@ int mpcb_plan_routes_host(int device, int B, const double* start, const double* 
                  i_hp = put(8 * 3 * AS_MAX_HP * AS_MAX_OBS * (size_t)S), i_nhp = put(4 * AS_MAX_OBS * (size_t)S), i_nobs = put(4 * (size_t)S),
                  i_pts = put(8 * 3 * (size_t)P * NP), i_mpn = put(4 * (size_t)P), i_len = put(8 * (size_t)P), i_cc = put(16 * (size_t)P * NCC),
                  w_gh = put(8 * nB * max_open), w_g = put(8 * nB * max_open), w_x = put(8 * nB * max_open), w_y = put(8 * nB * max_open),
-                 w_t = put(8 * nB * max_open), w_pred = put(4 * nB * max_open), w_mp = put(4 * nB * max_open),
+                 w_t = put(8 * nB * max_open), w_pred = put(4 * nB * max_open), w_mp = put(4 * nB * max_open), w_bmin = put(8 * nB * ((size_t)max_open / AS_OB + 1)),
                  c_x = put(8 * nB * max_closed), c_y = put(8 * nB * max_closed), c_t = put(8 * nB * max_closed), c_g = put(8 * nB * max_closed),
                  c_pred = put(4 * nB * max_closed), c_mp = put(4 * nB * max_closed), w_hash = put(4 * nB * hash_cap),
                  o_status = put(4 * nB), o_cost = put(8 * nB), o_npath = put(4 * nB), o_seq = put(4 * nB * max_path),
@@ -392,7 +424,7 @@ int mpcb_plan_routes_host(int device, int B, const double* start, const double* 
     p.obs_set = (int*)(d + i_set); p.hp = (double*)(d + i_hp); p.n_hp = (int*)(d + i_nhp); p.n_obs = (int*)(d + i_nobs);
     p.mp_points = (double*)(d + i_pts); p.mp_n = (int*)(d + i_mpn); p.mp_len = (double*)(d + i_len); p.mp_cc = (double*)(d + i_cc);
     p.o_gh = (double*)(d + w_gh); p.o_g = (double*)(d + w_g); p.o_x = (double*)(d + w_x); p.o_y = (double*)(d + w_y); p.o_t = (double*)(d + w_t);
-    p.o_pred = (int*)(d + w_pred); p.o_mp = (int*)(d + w_mp);
+    p.o_pred = (int*)(d + w_pred); p.o_mp = (int*)(d + w_mp); p.o_bmin = (double*)(d + w_bmin);
     p.c_x = (double*)(d + c_x); p.c_y = (double*)(d + c_y); p.c_t = (double*)(d + c_t); p.c_g = (double*)(d + c_g);
     p.c_pred = (int*)(d + c_pred); p.c_mp = (int*)(d + c_mp); p.hash = (int*)(d + w_hash);
     p.status = (int*)(d + o_status); p.cost = (double*)(d + o_cost); p.n_path = (int*)(d + o_npath); p.mp_seq = (int*)(d + o_seq);

@@ -194,9 +194,26 @@ def _p(a):
 
 
 def plan_batch(scenarios: Sequence[Scenario], library: PrimitiveLibrary, margin: float, device: int = 0,
-               max_open: int = 65536, max_closed: int = 16384, max_path: int = 32, want_trajectory: bool = True) -> PlanResult:
+               max_open: int = 65536, max_closed: int = 16384, max_path: int = 32, want_trajectory: bool = True,
+               grow: int = 2) -> PlanResult:
     """A* for every scenario in one launch.  Scenarios that share their obstacle list (same list object) share one
-    half-plane set on the device."""
+    half-plane set on the device.  A search that runs out of open-list / closed-set capacity (PLAN_OVERFLOW) is run again,
+    alone with the other overflowed ones, at 4x the capacities, up to `grow` times: the capacities are a first guess, not
+    a limit of the planner (the reference's heap and dict grow as needed, main/lib/a_star.py:31-78)."""
+    res = _plan_once(scenarios, library, margin, device, max_open, max_closed, max_path, want_trajectory)
+    for _ in range(int(grow)):
+        ov = np.flatnonzero(res.status == PLAN_OVERFLOW)
+        if len(ov) == 0:
+            break
+        max_open, max_closed = 4 * max_open, 4 * max_closed
+        sub = _plan_once([scenarios[b] for b in ov], library, margin, device, max_open, max_closed, max_path, want_trajectory)
+        for name in ("status", "cost", "n_path", "mp_seq", "nodes", "n_expanded", "n_pushed", "traj", "n_traj"):
+            if getattr(res, name) is not None:
+                getattr(res, name)[ov] = getattr(sub, name)
+    return res
+
+
+def _plan_once(scenarios, library, margin, device, max_open, max_closed, max_path, want_trajectory) -> PlanResult:
     B = len(scenarios)
     sets, set_of, hp_list = {}, np.zeros(B, np.int32), []
     for b, sc in enumerate(scenarios):

@@ -109,7 +109,11 @@ def test_capacity_overflow_is_reported_not_silent():
     k = int(np.argmax(g["n_expanded"] * (g["failed"] == 0)))          # the longest recorded search
     sc = dataclasses.replace(planner.intersection(turn_indicator=int(g["turn"][k]), start_pos=int(g["start_pos"][k])),
                              start=tuple(g["start"][k]))
-    small = planner.plan_batch([sc], lib, margin=float(g["radius"]), max_open=512, max_closed=256)
+    small = planner.plan_batch([sc], lib, margin=float(g["radius"]), max_open=512, max_closed=256, grow=0)
     assert small.status[0] == planner.PLAN_OVERFLOW and small.n_path[0] == 0 and (small.mp_seq[0] == -1).all() and np.isnan(small.cost[0])
     ok = planner.plan_batch([sc], lib, margin=float(g["radius"]))
     assert ok.status[0] == planner.PLAN_OK and ok.cost[0] == g["cost"][k]
+    # the capacities are a first guess: with growth on, the same tiny start is re-run at 4x, 16x, ... and ends with the same answer
+    grown = planner.plan_batch([sc], lib, margin=float(g["radius"]), max_open=512, max_closed=256, grow=4)
+    assert grown.status[0] == planner.PLAN_OK and grown.cost[0] == g["cost"][k]
+    assert np.array_equal(grown.mp_seq[0], ok.mp_seq[0]) and grown.n_expanded[0] == ok.n_expanded[0]
