@@ -193,22 +193,17 @@ int launch_step_long_nt(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     h->launches++;
     return MPCB_OK;
 }
-// Threads per problem: T = 80 (122 KB of shared memory: one CTA per SM whatever its size) runs 61 % faster with 8 warps
-// sharing the rows of the trailing update than with 4 (29.0 K vs 18.0 K solves/s at B = 4096); T = 40 (30 KB, two
-// 248-register CTAs per SM either way) is faster with 4 (157 K vs 118 K).  Also measured and rejected: 512 threads at 128
-// registers (spills; 27.0 K at T = 80), register caps for 3 or 4 CTAs per SM at T = 40 (135 K / 162 K with spills).
+// Threads per problem (rows of the system matrix go to threads i % NT).  T = 80: 146 KB of shared memory = one CTA per SM
+// whatever its size; 8 warps sharing the tile updates and the row phases: 111 K solves/s, 4 warps: 97 K (B = 4096).  T = 40:
+// 48 KB per problem; 64 threads (4 CTAs per SM, every barrier stall of one problem hidden by three others): 766 K, 128
+// threads (2 CTAs per SM at 250 registers): 531 K; 128 threads capped at 168 / 128 registers (3 / 4 CTAs, spills): 512 K / 593 K.
 int launch_step_long(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     // threads per problem (MPCB_LONG_THREADS overrides, tuning only): rows of the system matrix go to threads i % NT
     static const int nt_env = getenv("MPCB_LONG_THREADS") ? atoi(getenv("MPCB_LONG_THREADS")) : 0;
-    static const int minb = getenv("MPCB_LONG_MINB") ? atoi(getenv("MPCB_LONG_MINB")) : 0;     // resident CTAs per SM asked of ptxas
     const int nthreads = nt_env ? nt_env : (h->cfg.T > 40 ? 256 : 64);
     if (nthreads == 256) return launch_step_long_nt<256>(h, p, st);
     if (nthreads == 64) return launch_step_long_nt<64, 4>(h, p, st);
-    switch (minb) {
-        case 2: return launch_step_long_nt<kLongThreads, 2>(h, p, st);
-        case 3: return launch_step_long_nt<kLongThreads, 3>(h, p, st);
-        default: return launch_step_long_nt<kLongThreads>(h, p, st);
-    }
+    return launch_step_long_nt<kLongThreads>(h, p, st);      // 128 threads: measured and rejected at T = 40 (profiles/r02_NOTES.md)
 }
 
 #ifdef MPCB_TRACE

@@ -167,15 +167,16 @@ def test_config3_as_benched_every_step_vs_port(routes_smooth):
     assert stats["p999_du0"] < 1e-6 and stats["max_du0"] < 1e-4
 
 
-@pytest.mark.parametrize("T,B,K", [(10, 8192, 13), (13, 8192, 13), (40, 8192, 13), (80, 4096, 25)])
-def test_config5_long_and_short_horizons_never_fail_where_the_port_solves(T, B, K):
+@pytest.mark.parametrize("T,B,K,L", [(10, 8192, 13, 2.86), (13, 8192, 13, 2.86), (40, 8192, 13, 2.86), (80, 4096, 25, 2.86),
+                                     (80, 65536, 11, 4.0)])      # the last one: the sweep's largest cell, Prius wheelbase
+def test_config5_long_and_short_horizons_never_fail_where_the_port_solves(T, B, K, L):
     """BASELINE.json configs[4] generator (cfg-2 problems at other horizons), >= 100 K solves per horizon from a cold
     start: every problem the kernel reports as failed is replayed through the port, which must fail it too (zero
     'kernel fails, port solves'); a sample of the solved ones is compared at 1e-6."""
     from mpc_for_av_at_intersection_b200.scenarios import make_workload
     cfg, cs, ses, cfgvec, mpc_port = _setup(T, B)
     wl = make_workload(cs, B, seed=1234 + 4)
-    ses.begin(wl["route"], target_ind=wl["target_ind"])
+    ses.begin(wl["route"], target_ind=wl["target_ind"], L=np.full(B, L))
     ses.store("state", wl["state"])
     rng = np.random.default_rng(T)
     failed = kernel_only = sampled = 0
@@ -188,7 +189,7 @@ def test_config5_long_and_short_horizons_never_fail_where_the_port_solves(T, B, 
         bad = np.flatnonzero(post["status"] == 2)
         failed += len(bad)
         if len(bad):
-            ref = _port_replay(mpc_port, cfgvec, cs, pre, cfg.wheelbase, sel=bad)
+            ref = _port_replay(mpc_port, cfgvec, cs, pre, L, sel=bad)
             wrong = bad[ref["status"] <= 1]
             if len(wrong):
                 _dump(f"kernel_only_failures_T{T}_step{k}.npz", pre, wrong,
@@ -196,7 +197,7 @@ def test_config5_long_and_short_horizons_never_fail_where_the_port_solves(T, B, 
             kernel_only += len(wrong)
         good = np.flatnonzero(post["status"] <= 1)
         sel = rng.choice(good, min(len(good), 48 if T >= 40 else 256), replace=False)
-        ref = _port_replay(mpc_port, cfgvec, cs, pre, cfg.wheelbase, sel=sel)
+        ref = _port_replay(mpc_port, cfgvec, cs, pre, L, sel=sel)
         both = ref["status"] <= 1
         assert both.mean() > 0.98
         assert np.array_equal(post["target_ind"][sel], ref["target"])
