@@ -8,6 +8,7 @@
 
 #include "../../include/mpcb.h"
 #include "mpcb_step.cuh"
+#include "mpcb_step_half.cuh"
 #include "mpcb_step_long.cuh"
 #include "mpcb_coupling.cuh"
 
@@ -169,6 +170,32 @@ int launch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     CUDA_TRY(h, cudaGetLastError());
     h->launches++;
     return MPCB_OK;
+}
+
+// Two problems per warp (mpcb_step_half.cuh): T + 1 <= 16.  MPCB_HALF_WARP=0 in the environment falls back to the lane-per-stage
+// kernel (A/B runs; read once).
+template <int T, int WARPS, int MINB, bool VAR = false>
+int launch_step_half(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
+    const size_t smem = 2 * sizeof(mpcb::WarpSmem<T>) * WARPS;
+    void (*kern)(const StepParams);
+    if constexpr (VAR) kern = mpcb::mpc_step_half_var_kernel<T, WARPS, MINB>;
+    else kern = mpcb::mpc_step_half_kernel<T, WARPS, MINB>;
+    static thread_local int configured_dev = -1;
+    if (configured_dev != h->device) {
+        CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        configured_dev = h->device;
+    }
+    const int warps = (p.B + 1) / 2;
+    const int grid = (warps + WARPS - 1) / WARPS;
+    kern<<<grid, WARPS * 32, smem, st>>>(p);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches++;
+    return MPCB_OK;
+}
+bool half_warp_enabled() {
+    static const bool on = [] { const char* e = getenv("MPCB_HALF_WARP"); return !(e && e[0] == '0'); }();
+    return on;
 }
 
 int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st);
@@ -500,15 +527,16 @@ int dispatch_step(mpcb_handle* h, const StepParams& p, cudaStream_t st) {
     if (h->cfg.jerk_model) return launch_step_long_nt<64, 4, true>(h, p, st);      // main/lib/mpc_jerk.py
     if (p.pw || p.vcut || p.ref_speed != 0.0) {        // controller variants: their own instantiation
         switch (h->cfg.T) {
-            case 10: return launch_step<10, 1, 8, true>(h, p, st);
-            case 13: return launch_step<13, 1, 8, true>(h, p, st);
+            case 10: return half_warp_enabled() ? launch_step_half<10, 1, 8, true>(h, p, st) : launch_step<10, 1, 8, true>(h, p, st);
+            case 13: return half_warp_enabled() ? launch_step_half<13, 1, 8, true>(h, p, st) : launch_step<13, 1, 8, true>(h, p, st);
             case 20: return launch_step<20, 1, 8, true>(h, p, st);
             default: break;                             // 40, 80: the long-horizon kernel carries them itself
         }
     }
     switch (h->cfg.T) {
-        case 10: return launch_step<10, 1, 8>(h, p, st);
+        case 10: return half_warp_enabled() ? launch_step_half<10, 1, 8>(h, p, st) : launch_step<10, 1, 8>(h, p, st);
         case 13:
+            if (half_warp_enabled()) return launch_step_half<13, 1, 8>(h, p, st);
 #ifdef MPCB_TUNE_VARIANTS
             switch (h->variant) {
                 case 1: return launch_step<13, 1, 168>(h, p, st);

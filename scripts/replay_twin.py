@@ -10,7 +10,7 @@ import condensed_model as cm
 from conftest import load_routes
 
 
-def build(d, i, T):
+def build(d, i, T, L=float(os.environ.get("REPLAY_L", "2.86"))):
     routes = load_routes(True)
     full = routes[int(d["route"][i])][: int(d["ncourse"][i])]
     x, y, yaw, v = d["state"][i]
@@ -19,8 +19,8 @@ def build(d, i, T):
     oa = d["oa"][i] if d["warm"][i] else np.zeros(T)
     od = d["odelta"][i] if d["warm"][i] else np.zeros(T)
     xref, tind, idx, re = mo.calc_ref_trajectory(x, y, v, full[:, 0], full[:, 1], full[:, 2], dl, 0.2, int(d["target_ind"][i]), T, None, None)
-    xbar = mo.predict_motion([x, y, v, yaw], list(oa), list(od), 2.86, 0.2, T)
-    c = cm.Condensed(xref, xbar, [x, y, v, yaw], re, cfg, 2.86, 0.2)
+    xbar = mo.predict_motion([x, y, v, yaw], list(oa), list(od), L, 0.2, T)
+    c = cm.Condensed(xref, xbar, [x, y, v, yaw], re, cfg, L, 0.2)
     return c, oa, od, (xref, xbar, [x, y, v, yaw], re, cfg)
 
 
@@ -30,7 +30,7 @@ if __name__ == "__main__":
     for i in ids:
         c, oa, od, raw = build(d, i, T)
         r = c.solve(oa, od, max_iter=60, verbose="-v" in sys.argv)
-        sol = mo.linear_mpc_control(*raw, 2.86, 0.2)
+        sol = mo.linear_mpc_control(*raw, float(os.environ.get("REPLAY_L", "2.86")), 0.2)
         print(f"problem {i}: twin status {r['status']} iters {r['iters']} u0=({r['od'][0]:.9f},{r['oa'][0]:.9f}); oracle:",
               None if sol is None else (sol["status"], sol["iters"], float(sol["od"][0]), float(sol["oa"][0])),
               "gpu iters", d["gpu_iters"][i] if "gpu_iters" in d.files else None,

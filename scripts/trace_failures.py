@@ -25,7 +25,8 @@ eng = BatchedMPC(cfg, CourseSet(load_intersection_routes()), B)
 trace = torch.zeros(B, 128, 8, dtype=torch.float64, device="cuda")
 eng._lib.mpcb_debug_set_trace.argtypes = [C.c_void_p]
 eng._lib.mpcb_debug_set_trace(C.c_void_p(trace.data_ptr()))
-out = eng.step_host(state, route, nc, tgt, warm, oa, od, di_ai, want_traj=False)
+Lw = np.full(B, float(os.environ.get("REPLAY_L", "2.86")))          # wheelbase of every replayed problem
+out = eng.step_host(state, route, nc, tgt, warm, oa, od, di_ai, L=Lw, want_traj=False)
 tr = trace.cpu().numpy()
 for b in range(B):
     print(f"== problem {b}: status {out['status'][b]} iters {out['iters'][b]} u0 = {di_ai[b]}")
