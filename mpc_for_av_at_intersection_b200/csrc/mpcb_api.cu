@@ -608,7 +608,11 @@ StepParams session_params(mpcb_handle* h) {
     // (8 per SM).  Measured with / without: B = 1024 (under one wave: order is irrelevant, the ordering pass is pure latency)
     // 4.27 / 4.54 M solves/s, 4096: 8.07 / 7.58, 8192: 8.83 / 8.53, 16384: 9.23 / 9.13, 32768: 9.44 / 9.45, 65536: 9.54 / 9.74
     static const int lpt_max_batch = getenv("MPCB_LPT_MAX_BATCH") ? atoi(getenv("MPCB_LPT_MAX_BATCH")) : 16384;
-    if (s.B > 8 * h->num_sms && s.B <= lpt_max_batch) { p.lpt_order = s.lpt_order; p.lpt_rank = s.lpt_rank; p.lpt_hist = s.lpt_hist; }
+    // The CTA-per-problem kernels (T = 40, 80, mpc_jerk) hold 4 or 1 problems per SM and run for milliseconds: the ordering pass
+    // is free there and the tail it removes is not (T = 40, B = 4096: 7 waves of problems that take 5..35 iterations).
+    const bool long_kernel = h->cfg.T > 31 || h->cfg.jerk_model;
+    const int resident = h->num_sms * (long_kernel ? (h->cfg.T > 40 ? 1 : 4) : 8);
+    if (s.B > resident && (long_kernel || s.B <= lpt_max_batch)) { p.lpt_order = s.lpt_order; p.lpt_rank = s.lpt_rank; p.lpt_hist = s.lpt_hist; }
     return p;
 }
 

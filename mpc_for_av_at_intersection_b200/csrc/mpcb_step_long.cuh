@@ -19,98 +19,105 @@
 namespace mpcb {
 
 // [phase: block primitives]
+// Cross-warp scratch in STATIC shared memory (compile-time addresses: no pointer registers, no address arithmetic), two
+// buffers used alternately: primitive k writes buffer k & 1, waits at its one barrier and reads; primitive k + 2 may overwrite
+// that buffer because every thread has passed the barrier of primitive k + 1 in between -- one __syncthreads per primitive
+// instead of two (the block primitives were 12-18 % of the kernel's samples, all of it barrier wait and address IMADs).
 template <int NT>
 struct BlockOps {
     static constexpr int NW = NT / 32;
-    double* red;      // NW + 2 doubles of scratch
-    int* redi;        // NW + 2 ints of scratch
-    int tid, lane, wid;
-    __device__ __forceinline__ BlockOps(double* r, int* ri) : red(r), redi(ri), tid(threadIdx.x), lane(threadIdx.x & 31), wid(threadIdx.x >> 5) {}
+    double (*red)[NW + 1];     // [2][NW + 1]
+    int (*redi)[NW + 1];
+    int tid, lane, wid, ph;
+    __device__ __forceinline__ BlockOps(double (*r)[NW + 1], int (*ri)[NW + 1])
+        : red(r), redi(ri), tid(threadIdx.x), lane(threadIdx.x & 31), wid(threadIdx.x >> 5), ph(0) {}
     // inclusive prefix sum over threads 0..tid
     __device__ __forceinline__ double scan_up(double v) {
+        double* const r = red[ph ^= 1];
         v = mpcb::scan_up(v, lane);
-        if (lane == 31) red[wid] = v;
+        if (lane == 31) r[wid] = v;
         __syncthreads();
         double off = 0.0;
 #pragma unroll
-        for (int w = 0; w < NW; ++w) off += (w < wid) ? red[w] : 0.0;
-        __syncthreads();
+        for (int w = 0; w < NW; ++w) off += (w < wid) ? r[w] : 0.0;
         return v + off;
     }
     // inclusive suffix sum over threads tid..NT-1
     __device__ __forceinline__ double scan_dn(double v) {
+        double* const r = red[ph ^= 1];
         v = mpcb::scan_dn(v, lane);
-        if (lane == 0) red[wid] = v;
+        if (lane == 0) r[wid] = v;
         __syncthreads();
         double off = 0.0;
 #pragma unroll
-        for (int w = 0; w < NW; ++w) off += (w > wid) ? red[w] : 0.0;
-        __syncthreads();
+        for (int w = 0; w < NW; ++w) off += (w > wid) ? r[w] : 0.0;
         return v + off;
     }
     __device__ __forceinline__ double sum(double v) {
+        double* const r = red[ph ^= 1];
         v = warp_sum(v);
-        if (lane == 0) red[wid] = v;
+        if (lane == 0) r[wid] = v;
         __syncthreads();
         double s = 0.0;
 #pragma unroll
-        for (int w = 0; w < NW; ++w) s += red[w];
-        __syncthreads();
+        for (int w = 0; w < NW; ++w) s += r[w];
         return s;
     }
     __device__ __forceinline__ double max(double v) {
+        double* const r = red[ph ^= 1];
         v = warp_max(v);
-        if (lane == 0) red[wid] = v;
+        if (lane == 0) r[wid] = v;
         __syncthreads();
-        double s = red[0];
+        double s = r[0];
 #pragma unroll
-        for (int w = 1; w < NW; ++w) s = fmax(s, red[w]);
-        __syncthreads();
+        for (int w = 1; w < NW; ++w) s = fmax(s, r[w]);
         return s;
     }
     // value of thread tid+1 (0 past the end) / tid-1 (0 before the start)
     __device__ __forceinline__ double dn1(double v) {
+        double* const r = red[ph ^= 1];
         double n = __shfl_down_sync(MPCB_FULL, v, 1);
-        if (lane == 0) red[wid] = v;
+        if (lane == 0) r[wid] = v;
         __syncthreads();
-        if (lane == 31) n = (wid + 1 < NW) ? red[wid + 1] : 0.0;
-        __syncthreads();
+        if (lane == 31) n = (wid + 1 < NW) ? r[wid + 1] : 0.0;
         return n;
     }
     __device__ __forceinline__ double up1(double v) {
+        double* const r = red[ph ^= 1];
         double n = __shfl_up_sync(MPCB_FULL, v, 1);
-        if (lane == 31) red[wid] = v;
+        if (lane == 31) r[wid] = v;
         __syncthreads();
-        if (lane == 0) n = (wid > 0) ? red[wid - 1] : 0.0;
-        __syncthreads();
+        if (lane == 0) n = (wid > 0) ? r[wid - 1] : 0.0;
         return n;
     }
     __device__ __forceinline__ int dn1i(int v) {
+        int* const r = redi[ph ^= 1];
         int n = __shfl_down_sync(MPCB_FULL, v, 1);
-        if (lane == 0) redi[wid] = v;
+        if (lane == 0) r[wid] = v;
         __syncthreads();
-        if (lane == 31) n = (wid + 1 < NW) ? redi[wid + 1] : 0;
-        __syncthreads();
+        if (lane == 31) n = (wid + 1 < NW) ? r[wid + 1] : 0;
         return n;
     }
     // block arg-min on (distance, index), ties to the lower index; every thread gets the winner's index
     __device__ __forceinline__ int argmin(double d, int i) {
+        ph ^= 1;
+        double* const r = red[ph];
+        int* const ri = redi[ph];
 #pragma unroll
         for (int o = 16; o >= 1; o >>= 1) {
             const double d2 = __shfl_xor_sync(MPCB_FULL, d, o);
             const int i2 = __shfl_xor_sync(MPCB_FULL, i, o);
             if (d2 < d || (d2 == d && i2 < i)) { d = d2; i = i2; }
         }
-        if (lane == 0) { red[wid] = d; redi[wid] = i; }
+        if (lane == 0) { r[wid] = d; ri[wid] = i; }
         __syncthreads();
-        d = red[0]; i = redi[0];
+        d = r[0]; i = ri[0];
 #pragma unroll
         for (int w = 1; w < NW; ++w) {
-            const double d2 = red[w];
-            const int i2 = redi[w];
+            const double d2 = r[w];
+            const int i2 = ri[w];
             if (d2 < d || (d2 == d && i2 < i)) { d = d2; i = i2; }
         }
-        __syncthreads();
         return i;
     }
 };
@@ -150,46 +157,46 @@ __device__ __forceinline__ int nearest_index_block(BlockOps<NT>& bo, const doubl
 // accumulator fragment of one mma.m8n8k4 (lane l <-> elements [l/4][2 (l%4)], [l/4][2 (l%4) + 1]: one conflict-free 16-byte
 // access per lane), a row chunk of a tile is what one thread of the lane-per-row phases reads.
 struct LongSmem {
+    // one base pointer and 32-bit offsets (in doubles): the interior-point loop is register-bound, ten generic pointers cost 20
     int T, n, nt;
-    double* M;        // nt (nt + 1) / 2 tiles x 64
-    double* Dinv;     // nt x 64: inverses of the unit-lower diagonal tiles of L (zero above the diagonal)
-    double* Lp;       // n x 4: -L of the current 4-column panel (rows above the trailing block are zero): A fragments
-    double* Wp;       // n x 4:  L D of the current panel (same zero rows): B fragments
-    double* vec;      // n      right-hand side / solution
-    double* dinv;     // n      1 / d_k
-    double* tab;      // NTAB x (T + 1) per-stage tables
-    double* red;      // scratch of the block primitives
-    int* redi;
-    static constexpr int NTAB = 24;
-    double* scr;      // jerk variant only: 2 (T + 1)^2 scratch of the pull-back through E
+    double* base;
+    int oM, oDinv, oLp, oWp, ovec, odinv, otab;
+    __device__ __forceinline__ double* scr() const { return base; }          // jerk variant only: 2 (T + 1)^2 scratch of the pull-back through E
+    __device__ __forceinline__ double* M() const { return base + oM; }       // nt (nt + 1) / 2 tiles x 64
+    __device__ __forceinline__ double* Dinv() const { return base + oDinv; } // nt x 64: inverses of the unit-lower diagonal tiles of L (zero above the diagonal)
+    __device__ __forceinline__ double* Lp() const { return base + oLp; }     // n x 4: -L of the current 4-column panel (rows above the trailing block are zero): A fragments
+    __device__ __forceinline__ double* Wp() const { return base + oWp; }     // n x 4:  L D of the current panel (same zero rows): B fragments
+    __device__ __forceinline__ double* vec() const { return base + ovec; }   // n      right-hand side / solution
+    __device__ __forceinline__ double* dinv() const { return base + odinv; } // n      1 / d_k
+    __device__ __forceinline__ double* tab() const { return base + otab; }   // NTAB x (T + 1) per-stage tables
+    static constexpr int NTAB = 26;
     __host__ __device__ static size_t unknowns(int T, bool jerk) { return jerk ? (size_t)((2 * T + 1 + 7) & ~7) : 2 * (size_t)T; }
     __host__ __device__ static size_t bytes(int T, int NT, bool jerk = false) {
         const size_t n = unknowns(T, jerk), nt = n / 8;
-        return (nt * (nt + 1) / 2 * 64 + nt * 64 + 8 * n + 2 * n + (size_t)NTAB * (T + 1) + NT / 32 + 4 +
-                (jerk ? 2 * (size_t)(T + 1) * (T + 1) : 0)) * sizeof(double) + (NT / 32 + 4) * sizeof(int);
+        (void)NT;
+        return (nt * (nt + 1) / 2 * 64 + nt * 64 + 8 * n + 2 * n + (size_t)NTAB * (T + 1) +
+                (jerk ? 2 * (size_t)(T + 1) * (T + 1) : 0)) * sizeof(double);
     }
     __device__ __forceinline__ void carve(unsigned char* raw, int T_, int NT, bool jerk = false) {
         T = T_; n = (int)unknowns(T_, jerk); nt = n >> 3;
-        double* q = reinterpret_cast<double*>(raw);
-        scr = q; if (jerk) q += 2 * (size_t)(T + 1) * (T + 1);
-        M = q; q += (size_t)nt * (nt + 1) / 2 * 64;
-        Dinv = q; q += (size_t)nt * 64;
-        Lp = q; q += 4 * n;
-        Wp = q; q += 4 * n;
-        vec = q; q += n;
-        dinv = q; q += n;
-        tab = q; q += (size_t)NTAB * (T + 1);
-        red = q; q += NT / 32 + 4;
-        redi = reinterpret_cast<int*>(q);
+        base = reinterpret_cast<double*>(raw);
+        int q = jerk ? 2 * (T + 1) * (T + 1) : 0;
+        oM = q; q += nt * (nt + 1) / 2 * 64;
+        oDinv = q; q += nt * 64;
+        oLp = q; q += 4 * n;
+        oWp = q; q += 4 * n;
+        ovec = q; q += n;
+        odinv = q; q += n;
+        otab = q;
     }
-    __device__ __forceinline__ double* t(int i) const { return tab + (size_t)i * (T + 1); }
-    __device__ __forceinline__ double* tile(int I, int J) const { return M + ((I * (I + 1) >> 1) + J) * 64; }
+    __device__ __forceinline__ double* t(int i) const { return base + otab + i * (T + 1); }
+    __device__ __forceinline__ double* tile(int I, int J) const { return base + oM + ((I * (I + 1) >> 1) + J) * 64; }
 };
 
 
 // table slots
 enum { LT_OA = 0, LT_TERM, LT_ZX, LT_ZY, LT_WX, LT_WY, LT_BB, LT_HH, LT_GAX, LT_GAY, LT_GCX, LT_GCY, LT_HA, LT_HC, LT_HB,
-       LT_DGA, LT_DGC, LT_WVS, LT_DA, LT_DC, LT_WRP, LT_U0, LT_U1, LT_SPARE };
+       LT_DGA, LT_DGC, LT_WVS, LT_DA, LT_DC, LT_WRP, LT_U0, LT_U1, LT_SPARE, LT_BESTA, LT_BESTD };
 
 // [phase: kernel head/inputs]
 // JERK = true: the controller variant main/lib/mpc_jerk.py -- a fifth state z, the integral of the
@@ -199,28 +206,29 @@ enum { LT_OA = 0, LT_TERM, LT_ZX, LT_ZY, LT_WX, LT_WY, LT_BB, LT_HH, LT_GAX, LT_
 // (prefix / suffix sums) and carries z_0 as unknown number 2T (n = 2T + 1, padded to a multiple of 8 with identity rows);
 // the jerk penalty (z_{t+1} - z_t)^2 = dt^2 a_t^2, t <= T - 2 (:190), is a diagonal input cost.  Derivation checked against the
 // goldens recorded from the unmodified module in oracle/condensed_jerk.py.
-template <int NT, int MINB = 1, bool JERK = false>
-__global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParams p, const int T) {
+// One CTA, one problem (b).  Returns the interior-point iterations of the solve (0 if the problem was skipped), block-uniform.
+template <int NT, bool JERK>
+__device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int T, const int b) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int b = blockIdx.x;
-    if (b >= p.B) return;
     LongSmem sm;
     sm.carve(smem_raw, T, NT, JERK);
-    BlockOps<NT> bo(sm.red, sm.redi);
+    __shared__ double s_red[2][NT / 32 + 1];
+    __shared__ int s_redi[2][NT / 32 + 1];
+    BlockOps<NT> bo(s_red, s_redi);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     constexpr int NW = NT / 32;
     const bool act = tid < T;
     const double dt = p.dt;
     const int n = sm.n;
 
-    if (p.done && p.done[b] != 0) return;
+    if (p.done && p.done[b] != 0) return 0;
     const double x0 = p.state[4 * b + 0], y0 = p.state[4 * b + 1], yaw0 = p.state[4 * b + 2], v0 = p.state[4 * b + 3];
     const int route = p.route[b];
     const int nc = p.ncourse[b];
     if (p.fuse_goal) {       // MPC.is_goal (main/lib/mpc.py:310-326)
         const double gd = hypot(x0 - p.goal[2 * b], y0 - p.goal[2 * b + 1]);
         const bool isgoal = gd <= p.goal_dis && abs(p.target_ind[b] - nc) < 5 && fabs(v0) <= p.stop_speed;
-        if (isgoal) { __syncthreads(); if (tid == 0) p.done[b] = 1; return; }
+        if (isgoal) { __syncthreads(); if (tid == 0) p.done[b] = 1; return 0; }
     }
     const double L = p.L ? p.L[b] : p.wheelbase;
     const double dl = p.dl[route];
@@ -232,27 +240,30 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
     double oa = (warm && act) ? p.oa[(size_t)b * T + tid] : 0.0;     // mpc.py:222-224
     double od = (warm && act) ? p.od[(size_t)b * T + tid] : 0.0;
 
-    constexpr bool VAR = true;      // the long-horizon kernel always carries the variants (it is not register-bound)
-    // cost weights: the handle's, or this problem's own row (VAR kernels only)
-    double w_perp = p.w_perp, w_para = p.w_para, R0 = p.R0, R1 = p.R1, Rd0 = p.Rd0, Rd1 = p.Rd1, Qv = p.Qv, Qyaw = p.Qyaw,
-           Qf0 = p.Qf0, Qf1 = p.Qf1, Qf2 = p.Qf2, Qf3 = p.Qf3;
-    int vcut = 0x7fffffff;
-    if constexpr (VAR) {
-        if (p.pw) {
-            const double* __restrict__ w = p.pw + 12 * (size_t)b;
-            w_perp = w[0]; w_para = w[1]; R0 = w[2]; R1 = w[3]; Rd0 = w[4]; Rd1 = w[5]; Qv = w[6]; Qyaw = w[7];
-            Qf0 = w[8]; Qf1 = w[9]; Qf2 = w[10]; Qf3 = w[11];
-        }
-        if (p.vcut) vcut = p.vcut[b];
-    }
     double xr_v = 0.0;                                 // xref[2, lane]: speed reference (mpc_with_speed.py:104), else 0
     int status = MPCB_ST_OPTIMAL, iters = 0;
     bool solved = false, have_ov = false;
+    int cold_retry = 0;                                // 0: first attempt; else 1 + iterations of the failed attempt from carried multipliers
     double sx = 0.0, sy = 0.0, sv = 0.0, sph = 0.0;    // solution states at index tid (0..T)
     double xr_x = 0.0, xr_y = 0.0, xr_yaw = 0.0;       // xref at state index tid (0..T)
 
+    if (tid == 0) { double* st0 = sm.t(LT_SPARE); st0[0] = x0; st0[1] = y0; st0[2] = yaw0; st0[3] = v0; }   // read by predict (barriers in between)
     for (int pass = 0; pass < p.max_iter; ++pass) {
         // [phase: A2 A3 A4 A5 tables]
+        constexpr bool VAR = true;      // the long-horizon kernel always carries the variants (it is not register-bound)
+        // cost weights: the handle's, or this problem's own row.  Loaded per pass, not per kernel: ten of the twelve are dead after the
+        // A5 tables, and the interior-point loop below is register-bound (values that live across it are spilled in its hot loops)
+        double w_perp = p.w_perp, w_para = p.w_para, R0 = p.R0, R1 = p.R1, Rd0 = p.Rd0, Rd1 = p.Rd1, Qv = p.Qv, Qyaw = p.Qyaw,
+               Qf0 = p.Qf0, Qf1 = p.Qf1, Qf2 = p.Qf2, Qf3 = p.Qf3;
+        int vcut = 0x7fffffff;
+        if constexpr (VAR) {
+            if (p.pw) {
+                const double* __restrict__ w = p.pw + 12 * (size_t)b;
+                w_perp = w[0]; w_para = w[1]; R0 = w[2]; R1 = w[3]; Rd0 = w[4]; Rd1 = w[5]; Qv = w[6]; Qyaw = w[7];
+                Qf0 = w[8]; Qf1 = w[9]; Qf2 = w[10]; Qf3 = w[11];
+            }
+            if (p.vcut) vcut = p.vcut[b];
+        }
         // ---- A2: reference lookup (main/lib/mpc.py:86-109) ------------------------------------------------
         const int ni = nearest_index_block<NT>(bo, cx, cy, tind, nc, x0, y0);
         if (ni < 0) { status = MPCB_ST_NEAREST; break; }
@@ -382,12 +393,15 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             const double sa = bo.scan_up(a);
             const double bd_ = bb * d;
             const double sp_ = bo.scan_up(bd_);
-            vs = v0 + dt * sa;
-            phs = yaw0 + sp_;
-            const double vt = v0 + dt * (sa - a);
-            const double dph = (yaw0 + (sp_ - bd_)) - pb;
-            xs = x0 + bo.scan_up(c_ * vt - pp * dph);
-            ys = y0 + bo.scan_up(s_ * vt + qq * dph);
+            // the initial state from its table row (same values as x0..v0; a broadcast load per use instead of eight registers
+            // that would live across the whole interior-point loop)
+            const double* const st0 = sm.t(LT_SPARE);
+            vs = st0[3] + dt * sa;
+            phs = st0[2] + sp_;
+            const double vt = st0[3] + dt * (sa - a);
+            const double dph = (st0[2] + (sp_ - bd_)) - pb;
+            xs = st0[0] + bo.scan_up(c_ * vt - pp * dph);
+            ys = st0[1] + bo.scan_up(s_ * vt + qq * dph);
         };
         auto gradient = [&](double a, double d, double z0, double& ga, double& gd, double& gz) {
             double xs, ys, vs, phs;
@@ -444,6 +458,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             gscale = 1.0 + bo.max(fmax(fmax(fabs(g0a), fabs(g0d)), fabs(g0z)));
         }
         double s[8], lam[8];      // centred, gradient-scaled start: see mpcb_step.cuh
+        bool carried;
         {
             double g[8];
             G_apply(a, d, z0, g);
@@ -453,7 +468,8 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                 s[c] = mk[c] ? fmax(hh8[c] - g[c], 1.0) : 1.0;
                 lam[c] = mk[c] ? mu0 * rcp(s[c]) : 0.0;
             }
-            if (p.lam_ws && warm && pass == 0) {        // multipliers of the previous control step's solve, floored (mpcb_step.cuh)
+            carried = p.lam_ws && pass == 0 && !cold_retry && p.warm[b];
+            if (carried) {                              // multipliers of the previous control step's solve, floored (mpcb_step.cuh)
                 const double* __restrict__ lw = p.lam_ws + (size_t)b * 8 * T;
                 const double fl = fmax(1.0, 1e-5 * gscale);
 #pragma unroll
@@ -468,7 +484,10 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
         int it = 0;
         double mu_prev = 1e300;
         bool eta_safe = false;
-        double best_m = 1e300, best_a = 0.0, best_d = 0.0, best_z = 0.0;      // best iterate so far and its merit, see mpcb_step.cuh
+        // best iterate so far and its merit (see mpcb_step.cuh), kept in two table rows: a_t, d_t at [tid], z0 and the merit at [T]
+        // (touched once per iteration; as registers they would be live across the whole loop)
+        if (tid == 0) sm.t(LT_BESTD)[T] = 1e300;
+        __syncthreads();
         // [phase: residuals + tests]
         while (feasible0) {
             double rda, rdd, rdz, rp[8];
@@ -497,7 +516,12 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
 #endif
             {
                 const double m = fmax(fmax(res_d / (1e-8 * gscale), res_p * 1e9), mu * 1e9);
-                if (m < best_m && m < 100.0) { best_m = m; best_a = a; best_d = d; best_z = z0; }
+                const double bm = sm.t(LT_BESTD)[T];
+                __syncthreads();                         // every thread has read the old merit before thread 0 replaces it
+                if (m < bm && m < 100.0) {               // block-uniform
+                    if (act) { sm.t(LT_BESTA)[tid] = a; sm.t(LT_BESTD)[tid] = d; }
+                    if (tid == 0) { sm.t(LT_BESTA)[T] = z0; sm.t(LT_BESTD)[T] = m; }
+                }
             }
             if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) { converged = true; break; }
             if (it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) break;
@@ -521,8 +545,8 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
 #pragma unroll
                 for (int c = 0; c < 8; ++c) y[c] = lam[c] - w[c] * rp[c];
                 GT_apply(y, ya, yd, yz);
-                if (act) { sm.vec[tid] = ya - rda; sm.vec[T + tid] = yd - rdd; }
-                if constexpr (JERK) { if (tid >= 2 * T && tid < n) sm.vec[tid] = tid == 2 * T ? yz - rdz : 0.0; }
+                if (act) { sm.vec()[tid] = ya - rda; sm.vec()[T + tid] = yd - rdd; }
+                if constexpr (JERK) { if (tid >= 2 * T && tid < n) sm.vec()[tid] = tid == 2 * T ? yz - rdz : 0.0; }
             }
             __syncthreads();
             // [phase: assemble M]
@@ -533,8 +557,8 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                 // pulled back through e = E [a; z0]: P <- E' P E, B <- B E by running sums (T is small: one thread per row /
                 // column), then scattered with the input terms into the tiles; unknowns [a | delta | z0 | identity padding]
                 const int ld = T + 1;
-                double* P = sm.scr;                                // (T + 1) x (T + 1): rows / columns 0..T-1 = e, T = z0
-                double* Bq = sm.scr + ld * ld;                     // T x (T + 1): steer rows, columns as P
+                double* P = sm.scr();                                // (T + 1) x (T + 1): rows / columns 0..T-1 = e, T = z0
+                double* Bq = sm.scr() + ld * ld;                     // T x (T + 1): steer rows, columns as P
                 const double kA = 2.0 * dt * dt;
                 for (int idx = tid; idx < T * T; idx += NT) {
                     const int i = idx / T, j = idx - i * T, hi = max(i, j), lo = min(i, j);
@@ -644,8 +668,8 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                 bad = bad || !(m00 > 0.0 && d1 > 0.0 && d2 > 0.0 && d3 > 0.0 && i0 < 1e300 && i1 < 1e300 && i2 < 1e300 && i3 < 1e300);
                 for (int i = tid; i < n; i += NT) {                 // row i of the panel (threads take rows i, i + NT, ...)
                     if (i < k) continue;
-                    double2* lp = reinterpret_cast<double2*>(sm.Lp + 4 * i);
-                    double2* wp = reinterpret_cast<double2*>(sm.Wp + 4 * i);
+                    double2* lp = reinterpret_cast<double2*>(sm.Lp() + 4 * i);
+                    double2* wp = reinterpret_cast<double2*>(sm.Wp() + 4 * i);
                     if (i >= k + 4) {
                         double2* row = reinterpret_cast<double2*>(sm.tile(i >> 3, Kt) + (i & 7) * 8 + ko);
                         const double2 r01 = row[0], r23 = row[1];
@@ -660,7 +684,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                         lp[0] = make_double2(0.0, 0.0); lp[1] = make_double2(0.0, 0.0);
                         wp[0] = make_double2(0.0, 0.0); wp[1] = make_double2(0.0, 0.0);
                         const int a = i - k;
-                        sm.dinv[i] = a == 0 ? i0 : a == 1 ? i1 : a == 2 ? i2 : i3;
+                        sm.dinv()[i] = a == 0 ? i0 : a == 1 ? i1 : a == 2 ? i2 : i3;
                     }
                 }
                 __syncthreads();
@@ -679,10 +703,10 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                         const int rel = half == 0 ? pr : Rr - 1 - pr;
                         if (half == 1 && rel == pr) break;
                         const int I = Jmin + rel;
-                        const double afrag = sm.Lp[(8 * I + (lane >> 2)) * 4 + (lane & 3)];
+                        const double afrag = sm.Lp()[(8 * I + (lane >> 2)) * 4 + (lane & 3)];
                         // four tiles in flight: all loads, then the MMAs, then the stores (the tiles of a row are consecutive
                         // in memory; the compiler cannot prove that a store to one does not feed the next load)
-                        const double* wj = sm.Wp + (lane >> 2) * 4 + (lane & 3);
+                        const double* wj = sm.Wp() + (lane >> 2) * 4 + (lane & 3);
                         double2* Crow = reinterpret_cast<double2*>(sm.tile(I, 0) + (lane >> 2) * 8 + (lane & 3) * 2);
                         for (int J = Jmin; J <= I; J += 4) {
                             double bf[4];
@@ -721,7 +745,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
 #pragma unroll
                     for (int j = 0; j < r; ++j) acc = fma(-Lt[r * 8 + j], x[j], acc);
                     x[r] = acc;
-                    sm.Dinv[J * 64 + r * 8 + c] = acc;             // zero above the diagonal by construction
+                    sm.Dinv()[J * 64 + r * 8 + c] = acc;             // zero above the diagonal by construction
                 }
             }
             __syncthreads();
@@ -734,28 +758,28 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                         const bool mine = (tid >> 3) == (tj >> 3);
                         double z = 0.0;
                         if (mine) {
-                            const double* Li = sm.Dinv + J * 64 + (tid & 7) * 8;
-                            const double* v = sm.vec + 8 * J;
+                            const double* Li = sm.Dinv() + J * 64 + (tid & 7) * 8;
+                            const double* v = sm.vec() + 8 * J;
 #pragma unroll
                             for (int c = 0; c < 8; ++c) z = fma(Li[c], v[c], z);
                         }
                         __syncwarp();
-                        if (mine) sm.vec[8 * J + (tid & 7)] = z;
+                        if (mine) sm.vec()[8 * J + (tid & 7)] = z;
                     }
                     __syncthreads();
                     for (int i = tid; i < n; i += NT) {
                         if ((i >> 3) <= J) continue;
                         const double* row = sm.tile(i >> 3, J) + (i & 7) * 8;
-                        const double* v = sm.vec + 8 * J;
-                        double acc = sm.vec[i];
+                        const double* v = sm.vec() + 8 * J;
+                        double acc = sm.vec()[i];
 #pragma unroll
                         for (int c = 0; c < 8; ++c) acc = fma(-row[c], v[c], acc);
-                        sm.vec[i] = acc;
+                        sm.vec()[i] = acc;
                     }
                     __syncwarp();
                 }
                 __syncthreads();
-                for (int i = tid; i < n; i += NT) sm.vec[i] *= sm.dinv[i];
+                for (int i = tid; i < n; i += NT) sm.vec()[i] *= sm.dinv()[i];
                 __syncthreads();
                 for (int J = sm.nt - 1; J >= 0; --J) {             // backward: L' x = y
                     const int tj = (8 * J) % NT;
@@ -763,22 +787,22 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                         const bool mine = (tid >> 3) == (tj >> 3);
                         double z = 0.0;
                         if (mine) {
-                            const double* Lc = sm.Dinv + J * 64 + (tid & 7);
-                            const double* v = sm.vec + 8 * J;
+                            const double* Lc = sm.Dinv() + J * 64 + (tid & 7);
+                            const double* v = sm.vec() + 8 * J;
 #pragma unroll
                             for (int c = 0; c < 8; ++c) z = fma(Lc[c * 8], v[c], z);
                         }
                         __syncwarp();
-                        if (mine) sm.vec[8 * J + (tid & 7)] = z;
+                        if (mine) sm.vec()[8 * J + (tid & 7)] = z;
                     }
                     __syncthreads();
                     for (int i = tid; i < 8 * J; i += NT) {
                         const double* col = sm.tile(J, i >> 3) + (i & 7);
-                        const double* v = sm.vec + 8 * J;
-                        double acc = sm.vec[i];
+                        const double* v = sm.vec() + 8 * J;
+                        double acc = sm.vec()[i];
 #pragma unroll
                         for (int c = 0; c < 8; ++c) acc = fma(-col[c * 8], v[c], acc);
-                        sm.vec[i] = acc;
+                        sm.vec()[i] = acc;
                     }
                     __syncwarp();
                 }
@@ -791,8 +815,8 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             double sigma_mu;
             {
                 solve();
-                const double da = act ? sm.vec[tid] : 0.0, dd = act ? sm.vec[T + tid] : 0.0;
-                const double dz = JERK ? sm.vec[2 * T] : 0.0;
+                const double da = act ? sm.vec()[tid] : 0.0, dd = act ? sm.vec()[T + tid] : 0.0;
+                const double dz = JERK ? sm.vec()[2 * T] : 0.0;
                 double g[8];
                 G_apply(da, dd, dz, g);
                 double tmax = 0.0;
@@ -822,12 +846,12 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
                     y[c] = rc[c] * sinv[c] - w[c] * rp[c];
                 }
                 GT_apply(y, ya, yd, yz);
-                if (act) { sm.vec[tid] = ya - rda; sm.vec[T + tid] = yd - rdd; }
-                if constexpr (JERK) { if (tid >= 2 * T && tid < n) sm.vec[tid] = tid == 2 * T ? yz - rdz : 0.0; }
+                if (act) { sm.vec()[tid] = ya - rda; sm.vec()[T + tid] = yd - rdd; }
+                if constexpr (JERK) { if (tid >= 2 * T && tid < n) sm.vec()[tid] = tid == 2 * T ? yz - rdz : 0.0; }
                 __syncthreads();
                 solve();
-                const double da = act ? sm.vec[tid] : 0.0, dd = act ? sm.vec[T + tid] : 0.0;
-                const double dz = JERK ? sm.vec[2 * T] : 0.0;
+                const double da = act ? sm.vec()[tid] : 0.0, dd = act ? sm.vec()[T + tid] : 0.0;
+                const double dz = JERK ? sm.vec()[2 * T] : 0.0;
                 double g[8];
                 G_apply(da, dd, dz, g);
                 double tmax = 0.0;
@@ -856,9 +880,24 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
             ++it;
         }
         // [phase: epilogue]
-        iters = it;
+        iters = it + (cold_retry ? cold_retry - 1 : 0);
         if (converged) status = MPCB_ST_OPTIMAL;
-        else if (feasible0 && best_m < 100.0) { status = best_m < 1.0 ? MPCB_ST_OPTIMAL : MPCB_ST_INACCURATE; a = best_a; d = best_d; z0 = best_z; }
+        else if (feasible0 && sm.t(LT_BESTD)[T] < 100.0) {
+            status = sm.t(LT_BESTD)[T] < 1.0 ? MPCB_ST_OPTIMAL : MPCB_ST_INACCURATE;
+            a = act ? sm.t(LT_BESTA)[tid] : 0.0; d = act ? sm.t(LT_BESTD)[tid] : 0.0; z0 = sm.t(LT_BESTA)[T];
+        }
+        else if (carried && feasible0) {
+            // The multipliers carried over from the previous control step save an iteration on almost every solve, but they are
+            // the wrong start when the active set flips (a vehicle far off its path whose saturated steering changes sign: every
+            // steer-bound multiplier of the old solve is ~1e5 on the wrong side, the iteration unwinds them through W = lam / s
+            // ratios of 1e17 and the unpivoted LDL' breaks down before any iterate is acceptable: 2 solves in 720,896 at T = 80,
+            // L = 4.0, tests/test_gpu_bench_workloads.py).  Such a solve is repeated from the cold centred start -- the start
+            // the CPU port and the reference always use -- by running this pass again (block-uniform: converged / best_m are).
+            cold_retry = 1 + it;
+            tind = p.target_ind[b];                     // the pass starts from the object's index again (A2 is not idempotent)
+            --pass;
+            continue;
+        }
         else { status = MPCB_ST_FAILED; solved = false; break; }
         solved = true;
         oa = a; od = d;
@@ -879,7 +918,7 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
     // ---- A7: bookkeeping of MPC.step (main/lib/mpc.py:289-299) -------------------------------------------------
     if (status == MPCB_ST_NEAREST) {
         if (tid == 0) { p.status[b] = status; if (p.iters) p.iters[b] = 0; if (p.fuse_plant && p.done) p.done[b] = 2; }
-        return;
+        return 0;
     }
     const size_t tb = (size_t)b * 4 * (T + 1);
     if (p.xref && tid <= T) {
@@ -901,10 +940,10 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
         for (int r = 0; r < 4; ++r) p.traj[tb + r * (T + 1) + tid] = qnan;
     }
     // applied controls: first stage of the solution, else the reference's fallback (mpc.py:294-297)
-    if (tid == 0) { sm.vec[0] = od; sm.vec[1] = oa; }
+    if (tid == 0) { sm.vec()[0] = od; sm.vec()[1] = oa; }
     __syncthreads();
-    const double di = solved ? sm.vec[0] : p.di_ai[2 * b];
-    const double ai = solved ? sm.vec[1] : p.max_decel;
+    const double di = solved ? sm.vec()[0] : p.di_ai[2 * b];
+    const double ai = solved ? sm.vec()[1] : p.max_decel;
     double dev = qnan;
     if (solved && tind < nc) {      // get_current_xref_deviation (mpc.py:301-308)
         const double ang = cyaw[tind] + 3.141592653589793 / 2;
@@ -937,6 +976,18 @@ __global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParam
         if (tid < 4) p.state_out[4 * b + tid] = col;
         if (p.history && tid < 8) p.history[8 * (size_t)b + tid] = col;
     }
+    return iters;
+}
+
+// Launch order: longest first, as in the warp-per-problem kernels (lpt_finish, mpcb_step.cuh).  A launch is 7 (T = 40, B = 4096,
+// four CTAs per SM) to 28 (T = 80) waves of problems that take 5..35 interior-point iterations; in index order the long ones
+// that start late are the tail of the launch.  Block s works on problem lpt_order[s]; warp 0 files the iteration count.
+template <int NT, int MINB = 1, bool JERK = false>
+__global__ void __launch_bounds__(NT, MINB) mpc_step_long_kernel(const StepParams p, const int T) {
+    if (blockIdx.x >= p.B) return;
+    const int b = p.lpt_order ? p.lpt_order[blockIdx.x] : (int)blockIdx.x;
+    const int iters = mpc_step_long_body<NT, JERK>(p, T, b);
+    if (threadIdx.x < 32) lpt_finish(p, b, iters);
 }
 
 }  // namespace mpcb

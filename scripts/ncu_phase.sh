@@ -5,7 +5,7 @@ R=$1; K=${2:-mpc_step_kernelILi20ELi1ELi8}; NP=${3:-4096}; SRC=${4:-mpcb_step.cu
 W=$(mktemp -d)
 ncu -i $R --page source --csv --print-source sass > $W/sass.csv 2>/dev/null
 ncu -i $R --page raw --csv > $W/raw.csv
-(cd $W && cuobjdump -xelf all /root/repo/mpc_for_av_at_intersection_b200/libmpcb.so >/dev/null 2>&1 && nvdisasm -g mpcb_api.sm_100a.cubin > disall.txt)
+(cd $W && cuobjdump -xelf all ${NCU_PHASE_LIB:-/root/repo/mpc_for_av_at_intersection_b200/libmpcb.so} >/dev/null 2>&1 && nvdisasm -g mpcb_api.sm_100a.cubin > disall.txt)
 python - $W/disall.txt $K > $W/dis.txt <<'PY'
 import sys
 L=open(sys.argv[1]).read().split('\n')
