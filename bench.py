@@ -110,6 +110,16 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def step_kernel_name(T):
+    """The kernel mpcb_api.cu's dispatch_step launches for this horizon (default environment)."""
+    if T <= 15 and os.environ.get("MPCB_HALF_WARP", "1")[:1] != "0":
+        return f"mpcb::mpc_step_half_kernel<{T},1,8> (two problems per warp, one per half-warp; one warp per CTA, 8 CTAs/SM)"
+    if T <= 31:
+        return f"mpcb::mpc_step_kernel<{T},1,8> (one warp per problem, one warp per CTA, 8 CTAs/SM)"
+    nt = 256 if T > 40 else 64
+    return f"mpcb::mpc_step_long_kernel<{nt},{1 if T > 40 else 4},false> (one CTA of {nt} threads per problem, {1 if T > 40 else 4} CTAs/SM, longest-first launch order)"
+
+
 def workload_string(B, T):
     """config.workload, identical in both arms (the driver compares the strings)."""
     return (f"BASELINE.json configs[1]: {B} independent ego vehicles per GPU on randomised intersection scenarios "
@@ -337,8 +347,7 @@ def run_b200(args):
             "gpu_launches": launches,
             "roofline": {"bound": "fp64_fma", "achieved": ach_tflops, "peak": peak, "unit": "TFLOP/s",
                          "frac": ach_tflops / peak if peak else None, "traffic": ncu_traffic(B, T),
-                         "kernel": (f"mpcb::mpc_step_kernel<{T},1,8> (one warp per problem, one warp per CTA, 8 CTAs/SM)" if T <= 31
-                                    else f"mpcb::mpc_step_long_kernel<128> (one CTA per problem, T={T})"), "flops_per_solve": F,
+                         "kernel": step_kernel_name(T), "flops_per_solve": F,
                          "peak_source": "measured live (mpcb_measure_fp64_peak: register-resident DFMA chains)",
                          "hbm": {"achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
                                  "peak_source": "MEASURED_PEAKS.json hbm_gbs" if os.path.exists(

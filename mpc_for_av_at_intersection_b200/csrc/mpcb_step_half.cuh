@@ -57,6 +57,7 @@ __device__ __forceinline__ bool grp_any(bool v, int half) {             // any l
     return ((__ballot_sync(MPCB_FULL, v) >> (16 * half)) & 0xffffu) != 0;
 }
 
+// [phase: nearest idx]
 // main/lib/trajectories.py:100-126, forward=True, on one half-warp (see nearest_index_in_direction); executed by both
 // halves together: the loop bound is the longer of the two scans
 __device__ __forceinline__ int nearest_index_h(const double* __restrict__ cx, const double* __restrict__ cy, int start, int nc,
@@ -99,6 +100,7 @@ __device__ __forceinline__ int nearest_index_h(const double* __restrict__ cx, co
     return -1;
 }
 
+// [phase: G ops]
 template <int T>
 __device__ __forceinline__ void G_apply_h(double a, double d, double dt, int l, double (&g)[8]) {
     const double dn = shfl_dn1_h(d, l);
@@ -113,6 +115,7 @@ __device__ __forceinline__ void GT_apply_h(const double (&y)[8], double dt, int 
     gd = y[2] - y[3] - r + shfl_up1_h(r, l);
 }
 
+// [phase: kernel head/inputs]
 // One warp, two problems.  b_in: this half's problem or -1 (no problem for the slot).  Returns the interior-point iterations
 // this half's problem took (0 if it was skipped).
 template <int T, int WARPS, bool VAR>
@@ -168,6 +171,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
     double xr_x = 0.0, xr_y = 0.0, xr_yaw = 0.0;       // xref at state index l (0..T)
 
     for (int pass = 0; pass < p.max_iter; ++pass) {
+        // [phase: A2]
         // ---- A2: reference lookup -----------------------------------------------------------------
         const int ni = nearest_index_h(cx, cy, tind, nc, x0, y0, l);
         if (ni < 0) nearest_fail = true;                  // the reference raises (trajectories.py:120): reported at the end,
@@ -192,6 +196,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
         if constexpr (VAR) xr_v = idx < vcut ? p.ref_speed : 0.0;
         const bool reach = (idx == nc - 1);
 
+        // [phase: A3]
         // ---- A3: rollout of the previous (unshifted) solution: operating point (vbar, phibar) -------
         const double dcl = clampd(od, -p.max_steer, p.max_steer);
         const double tnd = act ? tan(dcl) : 0.0;
@@ -210,6 +215,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
             if (l == t + 1) pb = pcur;
         }
 
+        // [phase: A4/A5]
         // ---- A4: linearisation coefficients of stage `l` -----------------------------------------
         double sn, cs;
         sincos(pb, &sn, &cs);
@@ -240,6 +246,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
         const double ra_w = act ? (reach ? p.r_end : R0) : 0.0;     // mpc.py:177-180
         const double rd_w = act ? (reach ? p.r_end : R1) : 0.0;
 
+        // [phase: H build]
         // ---- condensed Hessian from suffix moments ----------------------------------------------------
         const double Zx = scan_up_h(c_, l), Zy = scan_up_h(s_, l);
         const double Wx = scan_up_h(-pp, l), Wy = scan_up_h(qq, l);
@@ -295,6 +302,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
         }
         __syncwarp();
         auto tld = [&](int i) { return act ? sm.tab[i][l] : 0.0; };
+        // [phase: predict/grad defs]
         // ---- linear prediction and objective gradient by scans ------------------------------------------
         // returns the states at index l+1 (lanes < T); see oracle/condensed_model.py states()/grad()
         auto predict = [&](double a, double d, double& xs, double& ys, double& vs, double& phs) {
@@ -330,6 +338,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
             gd = act ? bb * pph + 2.0 * rd_w * d + 2.0 * Rd1 * fd : 0.0;
         };
 
+        // [phase: ipm init + grad matvec]
         // ---- A6: interior point on  min J(u)  s.t.  G u <= h ----------------------------------------------
         double hh8[8];
         hh8[0] = p.max_accel; hh8[1] = -p.max_decel; hh8[2] = p.max_steer; hh8[3] = p.max_steer;
@@ -418,6 +427,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
         // outer one runs while either half is still iterating, the inner one is left as soon as either half needs fresh
         // residuals (the other half gets an extra evaluation, which is harmless).  `stop` freezes a half: from then on its
         // bookkeeping (iteration count, status flags, best iterate, committed answer) is not touched any more.
+        // [phase: residuals (outer loop)]
         bool stop = !feasible0 || failed || nearest_fail;
         while (__any_sync(MPCB_FULL, !stop)) {
             {
@@ -446,6 +456,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
                     }
                 }
             }
+        // [phase: gap + stopping tests]
         for (;;) {
             {
                 double sl = 0.0;
@@ -466,6 +477,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
             }
             if (__any_sync(MPCB_FULL, leave) || !__any_sync(MPCB_FULL, !stop)) break;
 
+            // [phase: W, rhs]
             // ---- M = H + G' W G into registers (rows `l` of A, B, C) ---------------------------------
             double sinv[8], w[8];
 #pragma unroll
@@ -488,6 +500,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
                 GT_apply_h<T>(y, dt, l, ya, yd);
                 ra = ya - rda; rdl = yd - rdd;
             }
+            // [phase: factor driver+syrk]
             // ---- LDL' of M = H + G'WG, forward solve of the predictor right-hand side fused -------------------
             bool bad = false;
             double inva = 0.0, invd = 0.0;
@@ -596,6 +609,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
                 if (__any_sync(MPCB_FULL, leave2) || !__any_sync(MPCB_FULL, !stop)) break;
             }
             if (!act) { ra = 0.0; rdl = 0.0; }
+            // [phase: solves]
             // Triangular solves with the pivots in rolled loops.  The factor blocks are zero on and above the diagonal,
             // so every step is shuffle -> FMA with no predicate; the running right-hand sides are kept PRE-SCALED by
             // 1/d_i (the coefficient is scaled instead, off the dependency chain), which makes the value a l
@@ -643,6 +657,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
                 fa = ga; fd = gd;                              // = D^-1 L^-1 r
             };
 
+            // [phase: predictor+corrector]
             // ---- predictor (ph = 0) and corrector (ph = 1): one copy of the back solve, the G product and the ratio test ----
             // (a rolled two-pass loop: the hot loop body must stay inside the 32 KB instruction cache)
             double dsa[8], dla[8], rc[8];
@@ -715,6 +730,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
             if (__any_sync(MPCB_FULL, want)) break;
         }
         }
+        // [phase: epilogue]
         // OPTIMAL: the configured tolerances, or -- when the loop ended first -- a verified iterate of at least the 1e-8
         // class that the reference's ECOS calls optimal; INACCURATE: ECOS's reduced class (both accepted, mpc.py:196)
         bool ok = !failed && !nearest_fail;
@@ -825,6 +841,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
     return iters;
 }
 
+// [phase: launch order]
 // ---- launch order and kernels: slot s of the launch order is half (s & 1) of warp (s >> 1) -------------------------------
 // Neighbouring slots of the longest-first order (lpt_finish, mpcb_step.cuh) took the same number of iterations at the previous
 // control step, so the two problems of a warp mostly stop together.
