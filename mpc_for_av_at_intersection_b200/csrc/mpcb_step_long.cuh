@@ -152,6 +152,20 @@ __device__ __forceinline__ int nearest_index_block(BlockOps<NT>& bo, const doubl
     return -1;
 }
 
+// rank-4 update of N consecutive tiles of one tile row: C_u -= L_I (LD)_u', N tiles in flight (all loads, then the MMAs, then the
+// stores: the tiles of a row are consecutive in memory, the compiler cannot prove that a store to one does not feed the next load)
+template <int N>
+__device__ __forceinline__ void dmma_tiles(const double* __restrict__ wp, double2* cp, const double afrag) {
+    double bf[N];
+    double2 c[N];
+#pragma unroll
+    for (int u = 0; u < N; ++u) { bf[u] = wp[32 * u]; c[u] = cp[32 * u]; }
+#pragma unroll
+    for (int u = 0; u < N; ++u) dmma_m8n8k4(c[u].x, c[u].y, afrag, bf[u]);
+#pragma unroll
+    for (int u = 0; u < N; ++u) cp[32 * u] = c[u];
+}
+
 // shared-memory carve-up of one problem (doubles).  The system matrix M = H + G'WG (n = 2T unknowns, n a multiple of 8) is
 // kept as its LOWER 8x8 tiles, tile (I, J <= I) at M + (I (I + 1) / 2 + J) * 64, row-major inside a tile: a tile is the
 // accumulator fragment of one mma.m8n8k4 (lane l <-> elements [l/4][2 (l%4)], [l/4][2 (l%4) + 1]: one conflict-free 16-byte
@@ -708,21 +722,15 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
                         // in memory; the compiler cannot prove that a store to one does not feed the next load)
                         const double* wj = sm.Wp() + (lane >> 2) * 4 + (lane & 3);
                         double2* Crow = reinterpret_cast<double2*>(sm.tile(I, 0) + (lane >> 2) * 8 + (lane & 3) * 2);
-                        for (int J = Jmin; J <= I; J += 4) {
-                            double bf[4];
-                            double2 c[4];
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) {
-                                const int Ju = min(J + u, I);
-                                bf[u] = wj[32 * Ju];
-                                c[u] = Crow[32 * Ju];
-                            }
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) dmma_m8n8k4(c[u].x, c[u].y, afrag, bf[u]);
-#pragma unroll
-                            for (int u = 0; u < 4; ++u)
-                                if (J + u <= I) Crow[32 * (J + u)] = c[u];
-                        }
+                        // tiles Jmin..I of this row, four at a time, then the remainder: fixed offsets inside a group, two pointer
+                        // increments per group (the first version clamped and predicated every tile index: 15 instructions per DMMA)
+                        const double* wp = wj + 32 * Jmin;
+                        double2* cp = Crow + 32 * Jmin;
+                        int cnt = I - Jmin + 1;
+                        for (; cnt >= 4; cnt -= 4, wp += 128, cp += 128) dmma_tiles<4>(wp, cp, afrag);
+                        if (cnt == 3) dmma_tiles<3>(wp, cp, afrag);
+                        else if (cnt == 2) dmma_tiles<2>(wp, cp, afrag);
+                        else if (cnt == 1) dmma_tiles<1>(wp, cp, afrag);
                         if (ko == 0 && I == Kt) { __syncwarp(); if (lane == 0) write_pivot_block(); }
                     }
                 }
