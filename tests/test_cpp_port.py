@@ -18,7 +18,8 @@ def _courses():
     return CourseSet(load_routes(False))
 
 
-@pytest.mark.parametrize("name,T", [("random_T13.npz", 13), ("random_T20.npz", 20), ("closed_loop_T20.npz", 20), ("random_T40.npz", 40)])
+@pytest.mark.parametrize("name,T", [("random_T13.npz", 13), ("random_T20.npz", 20), ("closed_loop_T20.npz", 20), ("random_T40.npz", 40),
+                                    ("edge_cases_T10.npz", 10), ("edge_cases_T13.npz", 13), ("edge_cases_T20.npz", 20)])     # edge cases: raised / infeasible / cut paths
 def test_cpp_port_matches_reference_golden(name, T):
     import mpc_port
     from mpc_for_av_at_intersection_b200 import MpcConfig
@@ -26,7 +27,7 @@ def test_cpp_port_matches_reference_golden(name, T):
     cs = _courses()
     cfgvec = mpc_port.pack_config(MpcConfig.from_json(T=T))
     n = len(g["state"])
-    sel = np.arange(0, n, 2 if T <= 20 else 3)
+    sel = np.arange(0, n, 1 if name.startswith("edge") else (2 if T <= 20 else 3))
     state = np.ascontiguousarray(g["state"][sel])
     route = g["route"][sel].astype(np.int32)
     ncourse = g["ncourse"][sel].astype(np.int32)

@@ -181,6 +181,42 @@ def test_mpc_sensitivity_variant_is_one_batch():
     _compare(g40, sel, out, 40)
 
 
+@pytest.mark.parametrize("T", [10, 13, 20])
+def test_edge_cases_next_to_ordinary_problems(T):
+    """tests/golden/edge_cases_T*.npz (oracle/gen_golden_edge_cases.py, recorded from the unmodified reference): 95 problems in
+    which every second one leaves MPC.step by an unusual exit -- the nearest-index Exception (16), an infeasible solve (16),
+    a path cut to 1-2 points, the end of the path -- next to ordinary ones.  At T = 10 / 13 neighbours share a warp
+    (mpcb_step_half.cuh runs them in lockstep; no launch reordering at this batch size), so a stopped, failed or raising
+    half sits beside one that iterates on; 95 is odd, the last warp has one live half.  Exception class, failure class and
+    integer outputs identical, what the reference leaves untouched is untouched, solved controls within 1e-6."""
+    g = golden(f"edge_cases_T{T}.npz")
+    n = len(g["state"])
+    eng, cfg = _engine(T, n)
+    sel = np.arange(n)
+    out = _run_host(eng, g, sel)
+    raised, solved = g["raised"].astype(bool), g["solved"].astype(bool)
+    failed = ~raised & ~solved
+    assert raised.sum() >= 10 and failed.sum() >= 10
+    assert np.array_equal(out["status"] == 3, raised), "nearest-index Exception class"
+    assert np.array_equal(out["status"] <= 1, solved) and np.array_equal(out["status"] == 2, failed)
+    assert np.array_equal(out["target"], g["target_out"]), "target_ind (unchanged where the reference raised)"
+    ok = ~raised
+    assert np.array_equal(out["xref"][ok], g["xref"][ok])
+    # raised: nothing of the object changes (di, ai, warm start)
+    assert np.array_equal(out["di_ai"][raised, 0], g["di_in"][raised]) and np.array_equal(out["di_ai"][raised, 1], g["ai_in"][raised])
+    assert np.array_equal(out["warm"][raised], g["has_warm"][raised].astype(np.int32))
+    # failed: di kept, ai = MAX_DECEL, warm start dropped (mpc.py:294-297)
+    assert np.array_equal(out["di_ai"][failed, 0], g["di_in"][failed]) and np.all(out["di_ai"][failed, 1] == -10.0)
+    assert not out["warm"][failed].any() and out["warm"][solved].all()
+    s = solved
+    e_u0 = max(np.abs(out["di_ai"][s, 0] - g["di"][s]).max(), np.abs(out["di_ai"][s, 1] - g["ai"][s]).max())
+    e_u = max(np.abs(out["oa"][s] - g["oa"][s]).max(), np.abs(out["od"][s] - g["od"][s]).max())
+    tr = out["traj"][s]
+    e_x = max(np.abs(tr[:, 0] - g["ox"][s]).max(), np.abs(tr[:, 1] - g["oy"][s]).max(), np.abs(tr[:, 3] - g["oyaw"][s]).max())
+    print(f"T={T}: {n} problems ({raised.sum()} raise, {failed.sum()} fail): max|du0|={e_u0:.2e} max|du|={e_u:.2e} max|dxy,yaw|={e_x:.2e}")
+    assert e_u0 < 1e-6 and e_u < 2e-4 and e_x < 1e-5
+
+
 def test_mpc_jerk_variant_matches_reference():
     """main/lib/mpc_jerk.py (NX = 5: the acceleration input is also integrated into a fifth state with a free initial value
     that feeds the speed, jerk penalty, its hard-coded weights) through the jerk instantiation of the CTA-per-problem

@@ -31,7 +31,8 @@ def _replay(g, k, routes_smooth, T):
 
 @pytest.mark.parametrize("name,T,stride", [("random_T13.npz", 13, 3), ("random_T20.npz", 20, 4),
                                            ("closed_loop_T13.npz", 13, 5), ("closed_loop_T20.npz", 20, 6),
-                                           ("random_T40.npz", 40, 8), ("closed_loop_T80.npz", 80, 10)])
+                                           ("random_T40.npz", 40, 8), ("closed_loop_T80.npz", 80, 10),
+                                           ("edge_cases_T10.npz", 10, 1), ("edge_cases_T13.npz", 13, 2)])
 def test_oracle_matches_reference_golden(name, T, stride, routes_smooth):
     g = golden(name)
     n = len(g["state"])
