@@ -192,7 +192,8 @@ class Condensed:
         return A, C
 
     # ---- Mehrotra predictor-corrector, the iteration the kernel runs
-    def solve(self, a0=None, d0=None, tol_mu=1e-12, tol_p=1e-10, tol_d=1e-9, max_iter=40, verbose=False, eta_fn=None, init=None, warm=None):
+    def solve(self, a0=None, d0=None, tol_mu=1e-12, tol_p=1e-10, tol_d=1e-9, max_iter=40, verbose=False, eta_fn=None, init=None, warm=None,
+              factor=None):
         """Stationarity test: |r_d| < tol_d + 1e-12 * (1 + |grad J(0)|_inf) (the gradient's rounding floor scales with it)."""
         T = self.T
         A, B, C = self.hessian()
@@ -237,7 +238,29 @@ class Condensed:
             WA, WC = self.GWG(w)
             M = H + np.block([[WA, np.zeros((T, T))], [np.zeros((T, T)), WC]])
             try:
-                Lc = np.linalg.cholesky(M)
+                if factor is None:
+                    Lc = np.linalg.cholesky(M)
+                    solveM = lambda rhs: np.linalg.solve(Lc.T, np.linalg.solve(Lc, rhs))
+                else:
+                    # experiment hook (scripts/fp32_factor_experiment.py): ("f32", k) = symmetric Jacobi scaling, Cholesky and
+                    # triangular solves in float32, k steps of iterative refinement against the float64 matrix
+                    _, nref = factor
+                    dsc = 1.0 / np.sqrt(np.diag(M))
+                    Ms = (M * dsc[:, None]) * dsc[None, :]
+                    L32 = np.linalg.cholesky(Ms.astype(np.float32))
+                    if not np.isfinite(L32).all():
+                        raise np.linalg.LinAlgError("float32 factor")
+
+                    def solve32(r):
+                        y = np.linalg.solve(L32, r.astype(np.float32))
+                        return np.linalg.solve(L32.T, y).astype(np.float64)
+
+                    def solveM(rhs, Ms=Ms, dsc=dsc):
+                        b = rhs * dsc
+                        x = solve32(b)
+                        for _ in range(nref):
+                            x = x + solve32(b - Ms @ x)
+                        return x * dsc
             except np.linalg.LinAlgError:
                 status = 0 if (res_d < 1e-7 * gscale and res_p < 1e-8 and mu < 1e-8) else 2
                 it -= 1
@@ -247,7 +270,7 @@ class Condensed:
                 y = np.where(msk, rc / s - w * rp, 0.0)
                 ya, yd = self.GT_apply(y)
                 rhs = np.concatenate([-rda + ya, -rdd + yd])
-                du = np.linalg.solve(Lc.T, np.linalg.solve(Lc, rhs))
+                du = solveM(rhs)
                 da_, dd_ = du[:T], du[T:]
                 ds = np.where(msk, -rp - self.G_apply(da_, dd_), 0.0)
                 dl = np.where(msk, -(rc + lam * ds) / s, 0.0)
