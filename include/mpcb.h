@@ -38,7 +38,8 @@ extern "C" {
 
 /* per-problem status written to status[B] */
 #define MPCB_ST_OPTIMAL 0     /* cvxpy.OPTIMAL            (main/lib/mpc.py:196)  */
-#define MPCB_ST_INACCURATE 1  /* THIS solver's reduced residual class (dual 1e-6 x gradient scale, primal 1e-7, gap 1e-7 on
+#define MPCB_ST_INACCURATE 1  /* THIS solver's reduced residual class (dual 1e-6 x gradient scale, primal 1e-7, gap 1e-7 x
+                                 max(1, 1e-4 gradient scale) -- ECOS too judges the gap relative to the objective -- on
                                  a verified iterate), accepted like cvxpy.OPTIMAL_INACCURATE is (ibid.).  It is an analogue, not
                                  ECOS's own class: cvxpy -> ECOS is absent from the reference tree and unpinned, so which
                                  problems ECOS would call inaccurate cannot be reproduced.  OPTIMAL (0) means the configured

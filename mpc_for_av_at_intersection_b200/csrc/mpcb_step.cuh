@@ -650,7 +650,12 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
         // without meeting the configured tolerances -- iteration cap, pivot breakdown of the unpivoted LDL' at extreme lam/s
         // ratios, a step poisoned by such a factorisation -- the answer is that iterate and ITS residual class, the way a
         // CPU interior point keeps its best point.  merit < 1: the 1e-8 class the reference's ECOS calls optimal;
-        // < 100: ECOS's reduced (OPTIMAL_INACCURATE) class, which main/lib/mpc.py:196 accepts too.
+        // < 100: ECOS's reduced (OPTIMAL_INACCURATE) class, which main/lib/mpc.py:196 accepts too.  The merit is
+        // max(r_d / (1e-8 gscale), r_p / 1e-9, mu / (1e-9 max(1, 1e-4 gscale))): dual residual and gap are judged relative to
+        // the size of the cost (gscale = 1 + |grad J(0)|_inf), as ECOS judges gap / |objective|: for a vehicle far off its
+        // path (gscale 1e5..1e7, multipliers of that order) an ABSOLUTE gap of 1e-7 means slacks of 1e-13 and lam / s ratios
+        // of 1e17 -- beyond what an unpivoted LDL' survives (one T = 80 solve in 1.1 M ended FAILED at mu = 2e-7 where the
+        // port reported its inaccurate class: scripts/triage_sweep_failures.py).
         // (the merit lives in shared memory too: the kernel sits at the 255-register limit and these values are touched
         // only where the residuals are fresh -- the first iteration, every sixteenth, and the end game)
         double& best_m = sm.bc[5][0];                   // warp-uniform: every lane writes the same value
@@ -678,7 +683,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 res_d = warp_max(fmax(fabs(rda), fabs(rdd)));
                 res_p = warp_max(rpm);
                 verified = true;
-                const double m = fmax(fmax(res_d * (1e8 * rcp(gscale)), res_p * 1e9), warp_sum(sl) / m_cnt * 1e9);
+                const double m = fmax(fmax(res_d * (1e8 * rcp(gscale)), res_p * 1e9), warp_sum(sl) / m_cnt * (1e9 * rcp(fmax(1.0, 1e-4 * gscale))));
                 if (m < best_m && m < 100.0) {
                     best_m = m;
                     if (act) { sm.bc[6][lane] = a; sm.bc[7][lane] = d; }

@@ -444,7 +444,7 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
                     sl += s[c] * lam[c];
                 }
                 const double rd_new = grp_max(fmax(fabs(ga + gta), fabs(gd + gtd))), rp_new = grp_max(rpm);
-                const double m = fmax(fmax(rd_new * (1e8 * rcp(gscale)), rp_new * 1e9), grp_sum(sl) / m_cnt * 1e9);
+                const double m = fmax(fmax(rd_new * (1e8 * rcp(gscale)), rp_new * 1e9), grp_sum(sl) / m_cnt * (1e9 * rcp(fmax(1.0, 1e-4 * gscale))));
                 const double bm = best_m;
                 __syncwarp();                            // every lane has read the old merit before any lane replaces it
                 if (!stop) {

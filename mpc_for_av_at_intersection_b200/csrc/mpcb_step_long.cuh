@@ -529,7 +529,7 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
             }
 #endif
             {
-                const double m = fmax(fmax(res_d / (1e-8 * gscale), res_p * 1e9), mu * 1e9);
+                const double m = fmax(fmax(res_d / (1e-8 * gscale), res_p * 1e9), mu * 1e9 / fmax(1.0, 1e-4 * gscale));
                 const double bm = sm.t(LT_BESTD)[T];
                 __syncthreads();                         // every thread has read the old merit before thread 0 replaces it
                 if (m < bm && m < 100.0) {               // block-uniform

@@ -262,7 +262,7 @@ class Condensed:
                             x = x + solve32(b - Ms @ x)
                         return x * dsc
             except np.linalg.LinAlgError:
-                status = 0 if (res_d < 1e-7 * gscale and res_p < 1e-8 and mu < 1e-8) else 2
+                status = 0 if (res_d < 1e-7 * gscale and res_p < 1e-8 and mu < 1e-8 * max(1.0, 1e-4 * gscale)) else 2      # gap relative to the cost scale, as in the kernels
                 it -= 1
                 break
 
