@@ -396,6 +396,15 @@ def run_sweep(args):
     w, _ = run_closed_loop_sweep(cfg, courses, 4096 * world, max(args.warmup, 3), seed=args.seed, chunk=args.chunk, rank=rank,
                                  world=world, device=local)
     gather_results({"steps_run": w["steps_run"]}, 4096 * world)
+    if world > 1:
+        # NCCL sets up its large-message path on the first big collective (one run measured 39 ms for the 2.7 GB gather at N = 2
+        # against 4.4 ms in the others): a 64 MB-per-rank all-gather outside the clock, so that the timed one is steady state
+        import torch.distributed as dist
+        big = torch.zeros(16 << 20, dtype=torch.float32, device=dev)
+        out = torch.empty(world * big.numel(), dtype=torch.float32, device=dev)
+        dist.all_gather_into_tensor(out, big)
+        torch.cuda.synchronize(dev)
+        del big, out
     del w
     barrier()
     host = None
