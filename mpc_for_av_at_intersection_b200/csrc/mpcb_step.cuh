@@ -291,8 +291,8 @@ __device__ __forceinline__ int nearest_index_in_direction(const double* __restri
                                                           const double* __restrict__ cy, int start, int nc,
                                                           double x, double y, int lane) {
     const int n = nc - start;
-    if (n <= 1) return start;
-    if (n == 2) return start + 1;
+    if (__any_sync(MPCB_FULL, n <= 1)) return start;          // votes: see mpc_step_body
+    if (__any_sync(MPCB_FULL, n == 2)) return start + 1;
     double bd[3] = {1e300, 1e300, 1e300};
     int bi[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
     for (int j = start + lane; j < nc; j += 32) {
@@ -359,14 +359,18 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
     const double dt = p.dt;
 
     // ---- problem inputs ------------------------------------------------------------------------
-    if (p.done && p.done[b] != 0) return 0;
+    // Every exit of this function and of its loops is taken on a VOTE (__any_sync): all lanes compute the same condition anyway,
+    // but only a vote result is provably warp-uniform to the compiler -- with plain conditions it guarded every group of
+    // shuffles below with a divergence check and an out-of-line slow path (24 BRA.DIV, 520 WARPSYNC, 11.9 K instead of
+    // ~7 K SASS instructions; the two-per-warp kernel, written with votes from the start, has none).
+    if (__any_sync(MPCB_FULL, p.done && p.done[b] != 0)) return 0;
     const double x0 = p.state[4 * b + 0], y0 = p.state[4 * b + 1], yaw0 = p.state[4 * b + 2], v0 = p.state[4 * b + 3];
     const int route = p.route[b];
     const int nc = p.ncourse[b];
     if (p.fuse_goal) {       // MPC.is_goal (main/lib/mpc.py:310-326) as the loop head of mpc_intersection.py:97
         const double gd = hypot(x0 - p.goal[2 * b], y0 - p.goal[2 * b + 1]);
         const bool isgoal = gd <= p.goal_dis && abs(p.target_ind[b] - nc) < 5 && fabs(v0) <= p.stop_speed;
-        if (isgoal) { if (lane == 0) p.done[b] = 1; return 0; }
+        if (__any_sync(MPCB_FULL, isgoal)) { if (lane == 0) p.done[b] = 1; return 0; }
     }
     const double L = p.L ? p.L[b] : p.wheelbase;
     const double dl = p.dl[route];
@@ -400,10 +404,10 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
         // [phase: A2]
         // ---- A2: reference lookup -----------------------------------------------------------------
         const int ni = nearest_index_in_direction(cx, cy, tind, nc, x0, y0, lane);
-        if (ni < 0) { status = MPCB_ST_NEAREST; break; }
+        if (__any_sync(MPCB_FULL, ni < 0)) { status = MPCB_ST_NEAREST; break; }
         tind = ni;
         double trav = 0.0;
-        if (!have_ov) {
+        if (!__any_sync(MPCB_FULL, have_ov)) {
             const double pstep = __dmul_rn(fabs(fmax(v0, p.min_ref_speed)), dt);    // |ov| * dt, mpc.py:96-98
             double acc = 0.0;
 #pragma unroll 1
@@ -666,7 +670,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
         // instruction cache: the inner loop leaves ("break") whenever it needs fresh residuals and the outer one re-enters it.
         // [phase: residuals (outer loop)]
         bool stop = !feasible0;
-        while (!stop) {
+        while (__any_sync(MPCB_FULL, !stop)) {
             {
                 double ga, gd, gta, gtd, g[8];
                 gradient(a, d, ga, gd);
@@ -703,11 +707,11 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 tr[0] = it; tr[1] = res_d; tr[2] = res_p; tr[3] = mu; tr[5] = verified ? 1.0 : 0.0; tr[7] = gscale;
             }
 #endif
-            if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) {
+            if (__any_sync(MPCB_FULL, res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu)) {
                 if (verified) { converged = true; stop = true; }
                 break;                                   // not verified: fresh residuals first
             }
-            if (broke || it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) {
+            if (__any_sync(MPCB_FULL, broke || it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15)) {
                 if (verified) stop = true;
                 break;
             }
@@ -970,18 +974,19 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
             // only extra evaluation); a degenerate one that keeps iterating gets a fresh residual every other iteration,
             // while H + G'WG is still well enough conditioned to correct it.
             since = (res_d < p.tol_d + 1e-12 * gscale) ? since + 1 : 0;
-            if ((it & 15) == 0 || since >= 2) { since = 0; break; }
+            if (__any_sync(MPCB_FULL, (it & 15) == 0 || since >= 2)) { since = 0; break; }
         }
         }
         // [phase: epilogue]
         iters = it;
         // OPTIMAL: the configured tolerances, or -- when the loop ended first -- a verified iterate of at least the 1e-8
         // class that the reference's ECOS calls optimal; INACCURATE: ECOS's reduced class (both accepted, mpc.py:196)
+        if (__any_sync(MPCB_FULL, !converged && !(feasible0 && best_m < 100.0))) { status = MPCB_ST_FAILED; solved = false; break; }
         if (converged) status = MPCB_ST_OPTIMAL;
-        else if (feasible0 && best_m < 100.0) {
+        else {
             status = best_m < 1.0 ? MPCB_ST_OPTIMAL : MPCB_ST_INACCURATE;
             if (act) { a = sm.bc[6][lane]; d = sm.bc[7][lane]; }
-        } else { status = MPCB_ST_FAILED; solved = false; break; }
+        }
         (void)broke;
         // solution of this pass: mpc.py:197-202
         solved = true;
@@ -1003,7 +1008,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
     }
 
     // ---- A7: bookkeeping of MPC.step (main/lib/mpc.py:289-299) -------------------------------------------
-    if (status == MPCB_ST_NEAREST) {          // the reference raises here: nothing of the object changes
+    if (__any_sync(MPCB_FULL, status == MPCB_ST_NEAREST)) {          // the reference raises here: nothing of the object changes
         if (lane == 0) { p.status[b] = status; if (p.iters) p.iters[b] = 0; if (p.fuse_plant && p.done) p.done[b] = 2; }
         return 0;
     }
@@ -1100,8 +1105,7 @@ __device__ __forceinline__ void lpt_finish(const StepParams& p, int b, int iters
         __threadfence();
         last = atomicAdd(&p.lpt_hist[64], 1) == p.B - 1;
     }
-    last = __shfl_sync(MPCB_FULL, last, 0);
-    if (!last) return;
+    if (!__any_sync(MPCB_FULL, last)) return;
     __threadfence();
     // exclusive prefix over the 64 bins, two per lane
     const int h0 = __ldcg(&p.lpt_hist[2 * lane]), h1 = __ldcg(&p.lpt_hist[2 * lane + 1]);
@@ -1128,7 +1132,7 @@ template <int T, int WARPS, int MINB>
 __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_kernel(const StepParams p) {
     int slot;
     const int b = lpt_problem_of_slot<WARPS>(p, slot);
-    if (b < 0) return;
+    if (__any_sync(MPCB_FULL, b < 0)) return;
     lpt_finish(p, b, mpc_step_body<T, WARPS, false>(p, b));
 }
 
@@ -1136,7 +1140,7 @@ template <int T, int WARPS, int REGS>
 __global__ void __maxnreg__(REGS) mpc_step_kernel_r(const StepParams p) {
     int slot;
     const int b = lpt_problem_of_slot<WARPS>(p, slot);
-    if (b < 0) return;
+    if (__any_sync(MPCB_FULL, b < 0)) return;
     lpt_finish(p, b, mpc_step_body<T, WARPS, false>(p, b));
 }
 
@@ -1146,7 +1150,7 @@ template <int T, int WARPS, int MINB>
 __global__ void __launch_bounds__(WARPS * 32, MINB) mpc_step_var_kernel(const StepParams p) {
     int slot;
     const int b = lpt_problem_of_slot<WARPS>(p, slot);
-    if (b < 0) return;
+    if (__any_sync(MPCB_FULL, b < 0)) return;
     lpt_finish(p, b, mpc_step_body<T, WARPS, true>(p, b));
 }
 
