@@ -127,8 +127,8 @@ template <int NT>
 __device__ __forceinline__ int nearest_index_block(BlockOps<NT>& bo, const double* __restrict__ cx,
                                                    const double* __restrict__ cy, int start, int nc, double x, double y) {
     const int n = nc - start;
-    if (n <= 1) return start;
-    if (n == 2) return start + 1;
+    if (__any_sync(MPCB_FULL, n <= 1)) return start;
+    if (__any_sync(MPCB_FULL, n == 2)) return start + 1;
     double bd[3] = {1e300, 1e300, 1e300};
     int bi[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
     for (int j = start + bo.tid; j < nc; j += NT) {
@@ -235,14 +235,15 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
     const double dt = p.dt;
     const int n = sm.n;
 
-    if (p.done && p.done[b] != 0) return 0;
+    // exits on votes, as in mpcb_step.cuh: block-uniform conditions that the compiler can then also PROVE warp-uniform
+    if (__any_sync(MPCB_FULL, p.done && p.done[b] != 0)) return 0;
     const double x0 = p.state[4 * b + 0], y0 = p.state[4 * b + 1], yaw0 = p.state[4 * b + 2], v0 = p.state[4 * b + 3];
     const int route = p.route[b];
     const int nc = p.ncourse[b];
     if (p.fuse_goal) {       // MPC.is_goal (main/lib/mpc.py:310-326)
         const double gd = hypot(x0 - p.goal[2 * b], y0 - p.goal[2 * b + 1]);
         const bool isgoal = gd <= p.goal_dis && abs(p.target_ind[b] - nc) < 5 && fabs(v0) <= p.stop_speed;
-        if (isgoal) { __syncthreads(); if (tid == 0) p.done[b] = 1; return 0; }
+        if (__any_sync(MPCB_FULL, isgoal)) { __syncthreads(); if (tid == 0) p.done[b] = 1; return 0; }
     }
     const double L = p.L ? p.L[b] : p.wheelbase;
     const double dl = p.dl[route];
@@ -280,7 +281,7 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
         }
         // ---- A2: reference lookup (main/lib/mpc.py:86-109) ------------------------------------------------
         const int ni = nearest_index_block<NT>(bo, cx, cy, tind, nc, x0, y0);
-        if (ni < 0) { status = MPCB_ST_NEAREST; break; }
+        if (__any_sync(MPCB_FULL, ni < 0)) { status = MPCB_ST_NEAREST; break; }
         tind = ni;
         double trav = 0.0;
         if (!have_ov) {
@@ -503,7 +504,7 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
         if (tid == 0) sm.t(LT_BESTD)[T] = 1e300;
         __syncthreads();
         // [phase: residuals + tests]
-        while (feasible0) {
+        while (__any_sync(MPCB_FULL, feasible0)) {
             double rda, rdd, rdz, rp[8];
             {
                 double ga, gd, gz, gta, gtd, gtz, g[8];
@@ -537,8 +538,8 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
                     if (tid == 0) { sm.t(LT_BESTA)[T] = z0; sm.t(LT_BESTD)[T] = m; }
                 }
             }
-            if (res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu) { converged = true; break; }
-            if (it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15) break;
+            if (__any_sync(MPCB_FULL, res_d < p.tol_d + 1e-12 * gscale && res_p < p.tol_p && mu < p.tol_mu)) { converged = true; break; }
+            if (__any_sync(MPCB_FULL, it >= p.ipm_max_iter || !(mu == mu) || mu < 1e-15)) break;
 
             // [phase: W, rhs]
             double sinv[8], w[8];
@@ -739,7 +740,7 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
 #ifdef MPCB_TRACE
             if (p.trace && tid == 0 && it < 128 && bad) p.trace[((size_t)b * 128 + it) * 8 + 6] = 1.0;
 #endif
-            if (bad) break;
+            if (__any_sync(MPCB_FULL, bad)) break;
             // [phase: diag tile inverses]
             // inverses of the unit-lower diagonal tiles (thread 8 J + c: column c of tile J), so that a block step of the
             // triangular solves is an 8-term dot product instead of 8 dependent steps
@@ -889,24 +890,26 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
         }
         // [phase: epilogue]
         iters = it + (cold_retry ? cold_retry - 1 : 0);
+        if (__any_sync(MPCB_FULL, !converged && !(feasible0 && sm.t(LT_BESTD)[T] < 100.0))) {
+            if (__any_sync(MPCB_FULL, carried && feasible0)) {
+                // The multipliers carried over from the previous control step save an iteration on almost every solve, but they are
+                // the wrong start when the active set flips (a vehicle far off its path whose saturated steering changes sign: every
+                // steer-bound multiplier of the old solve is ~1e5 on the wrong side, the iteration unwinds them through W = lam / s
+                // ratios of 1e17 and the unpivoted LDL' breaks down before any iterate is acceptable: 2 solves in 720,896 at T = 80,
+                // L = 4.0, tests/test_gpu_bench_workloads.py).  Such a solve is repeated from the cold centred start -- the start
+                // the CPU port and the reference always use -- by running this pass again (block-uniform: converged / best_m are).
+                cold_retry = 1 + it;
+                tind = p.target_ind[b];                 // the pass starts from the object's index again (A2 is not idempotent)
+                --pass;
+                continue;
+            }
+            status = MPCB_ST_FAILED; solved = false; break;
+        }
         if (converged) status = MPCB_ST_OPTIMAL;
-        else if (feasible0 && sm.t(LT_BESTD)[T] < 100.0) {
+        else {
             status = sm.t(LT_BESTD)[T] < 1.0 ? MPCB_ST_OPTIMAL : MPCB_ST_INACCURATE;
             a = act ? sm.t(LT_BESTA)[tid] : 0.0; d = act ? sm.t(LT_BESTD)[tid] : 0.0; z0 = sm.t(LT_BESTA)[T];
         }
-        else if (carried && feasible0) {
-            // The multipliers carried over from the previous control step save an iteration on almost every solve, but they are
-            // the wrong start when the active set flips (a vehicle far off its path whose saturated steering changes sign: every
-            // steer-bound multiplier of the old solve is ~1e5 on the wrong side, the iteration unwinds them through W = lam / s
-            // ratios of 1e17 and the unpivoted LDL' breaks down before any iterate is acceptable: 2 solves in 720,896 at T = 80,
-            // L = 4.0, tests/test_gpu_bench_workloads.py).  Such a solve is repeated from the cold centred start -- the start
-            // the CPU port and the reference always use -- by running this pass again (block-uniform: converged / best_m are).
-            cold_retry = 1 + it;
-            tind = p.target_ind[b];                     // the pass starts from the object's index again (A2 is not idempotent)
-            --pass;
-            continue;
-        }
-        else { status = MPCB_ST_FAILED; solved = false; break; }
         solved = true;
         oa = a; od = d;
         if (p.lam_ws && act) {
@@ -924,7 +927,7 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
     }
 
     // ---- A7: bookkeeping of MPC.step (main/lib/mpc.py:289-299) -------------------------------------------------
-    if (status == MPCB_ST_NEAREST) {
+    if (__any_sync(MPCB_FULL, status == MPCB_ST_NEAREST)) {
         if (tid == 0) { p.status[b] = status; if (p.iters) p.iters[b] = 0; if (p.fuse_plant && p.done) p.done[b] = 2; }
         return 0;
     }
