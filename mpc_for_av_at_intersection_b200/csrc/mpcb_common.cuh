@@ -106,6 +106,16 @@ __device__ __forceinline__ double rcp(double x) {
     return fma(r, t, r);
 }
 __device__ __forceinline__ double clampd(double v, double lo, double hi) { return fmax(fmin(v, hi), lo); }
+// max(a, b) for a running maximum `a` that is never NaN: a NaN `b` is dropped, as fmax drops it, but in 3 instructions (compare,
+// two selects) instead of fmax's 7 (DSETP.MAX, selects, NaN quieting, register moves): the ratio test of the interior point
+// takes 32 of them per lane and iteration
+__device__ __forceinline__ double dmax_run(double a, double b) { return b > a ? b : a; }
+// warp maximum of values none of which is NaN
+__device__ __forceinline__ double warp_max_nn(double v) {
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) v = dmax_run(v, __shfl_xor_sync(MPCB_FULL, v, d));
+    return v;
+}
 
 // Predicated 16-byte shared store (one lane publishes {x, y}); a plain `if (lane == k) ...` with several
 // statements compiles to a divergent branch, an unconditional store by all lanes doubles the LSU wavefronts.

@@ -931,9 +931,9 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                     dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
                     dla[c] = mk[c] ? -(rc[c] + lam[c] * dsa[c]) * sinv[c] : 0.0;   // rc = s lam in the predictor: -lam - w ds
                     const double linv = mk[c] ? rcp(lam[c]) : 0.0;
-                    tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
+                    tmax = dmax_run(dmax_run(tmax, -dsa[c] * sinv[c]), -dla[c] * linv);
                 }
-                tmax = warp_max(tmax);
+                tmax = warp_max_nn(tmax);
                 if (ph == 0) {
                     const double al = 1.0 / fmax(1.0, tmax);
                     double sl = 0.0;

@@ -53,6 +53,11 @@ __device__ __forceinline__ double grp_max(double v) {
     for (int d = MPCB_HW / 2; d >= 1; d >>= 1) v = fmax(v, __shfl_xor_sync(MPCB_FULL, v, d));
     return v;
 }
+__device__ __forceinline__ double grp_max_nn(double v) {              // no NaN among the inputs (see dmax_run)
+#pragma unroll
+    for (int d = MPCB_HW / 2; d >= 1; d >>= 1) v = dmax_run(v, __shfl_xor_sync(MPCB_FULL, v, d));
+    return v;
+}
 __device__ __forceinline__ bool grp_any(bool v, int half) {             // any lane of THIS half
     return ((__ballot_sync(MPCB_FULL, v) >> (16 * half)) & 0xffffu) != 0;
 }
@@ -685,9 +690,9 @@ __device__ __forceinline__ int mpc_step_half_body(const StepParams& p, const int
                     dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
                     dla[c] = mk[c] ? -(rc[c] + lam[c] * dsa[c]) * sinv[c] : 0.0;   // rc = s lam in the predictor: -lam - w ds
                     const double linv = mk[c] ? rcp(lam[c]) : 0.0;
-                    tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
+                    tmax = dmax_run(dmax_run(tmax, -dsa[c] * sinv[c]), -dla[c] * linv);
                 }
-                tmax = grp_max(tmax);
+                tmax = grp_max_nn(tmax);
                 if (ph == 0) {
                     const double al = 1.0 / fmax(1.0, tmax);
                     double sl = 0.0;

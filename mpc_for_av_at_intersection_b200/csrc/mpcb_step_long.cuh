@@ -834,7 +834,7 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
                     dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
                     dla[c] = mk[c] ? -lam[c] - w[c] * dsa[c] : 0.0;
                     const double linv = mk[c] ? rcp(lam[c]) : 0.0;
-                    tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
+                    tmax = dmax_run(dmax_run(tmax, -dsa[c] * sinv[c]), -dla[c] * linv);
                 }
                 tmax = bo.max(tmax);
                 const double al = 1.0 / fmax(1.0, tmax);
@@ -869,7 +869,7 @@ __device__ __forceinline__ int mpc_step_long_body(const StepParams& p, const int
                     dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
                     dla[c] = mk[c] ? -(rc[c] + lam[c] * dsa[c]) * sinv[c] : 0.0;
                     const double linv = mk[c] ? rcp(lam[c]) : 0.0;
-                    tmax = fmax(tmax, fmax(-dsa[c] * sinv[c], -dla[c] * linv));
+                    tmax = dmax_run(dmax_run(tmax, -dsa[c] * sinv[c]), -dla[c] * linv);
                 }
                 tmax = bo.max(tmax);
                 // adaptive fraction to the boundary, see mpcb_step.cuh
