@@ -337,7 +337,8 @@ template <int T>
 __device__ __forceinline__ void G_apply(double a, double d, double dt, int lane, double (&g)[8]) {
     const double dn = shfl_dn1(d, lane);
     const double dd = (lane < T - 1) ? dn - d : 0.0;
-    const double cs = dt * scan_up(a, lane);
+    const double sc = scan_up(a, lane);                              // (the scan is a warp primitive: never inside the select)
+    const double cs = lane < T ? dt * sc : 0.0;                      // every row is zero on the idle lanes (a = d = 0 there)
     g[0] = a; g[1] = -a; g[2] = d; g[3] = -d; g[4] = dd; g[5] = -dd; g[6] = cs; g[7] = -cs;
 }
 template <int T>
@@ -622,7 +623,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
         }
         // gradient inside the interior-point loop: g0 + H u from the stored cost Hessian (column j of every block is
         // read down the lanes; the transposed cross block along row `lane`)
-        const int grow = act ? lane : (lane & 15);
+        const int grow = act ? lane : (T >= 16 ? (lane & 15) : 0);
         auto gradient = [&](double a, double d, double& ga, double& gd) {
             using SMg = WarpSmem<T>;
             double sa = g0a, sd = g0d;
@@ -860,7 +861,7 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
             // so every step is shuffle -> FMA with no predicate; the running right-hand sides are kept PRE-SCALED by
             // 1/d_i (the coefficient is scaled instead, off the dependency chain), which makes the value a lane
             // broadcasts at its own step the finished unknown.
-            const int lrow = act ? lane : (lane & 15);
+            const int lrow = act ? lane : (T >= 16 ? (lane & 15) : 0);
             const double* const LAr = &sm.LA[SM::colL(lrow)];        // LAr[k] = (row k, column lane)
             const double* const LCr = &sm.LC[SM::colL(lrow)];
             const double* const LBr = &sm.LB[SM::colB(lrow)];        // LBr[k] = (steer row k, accel column lane)
@@ -909,7 +910,11 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
             // `ph` selects: +2 % at T = 20, +3 % at T = 13; it was a rolled loop while the instruction cache was the limiter)
             double dsa[8], dla[8], rc[8];
 #pragma unroll
-            for (int c = 0; c < 8; ++c) { rc[c] = mk[c] ? s[c] * lam[c] : 0.0; dsa[c] = 0.0; dla[c] = 0.0; }
+            // No masks in this phase: a row that does not exist on a lane (idle lanes, the last stage's rate rows) holds
+            // s = 1, lam = 0, r_p = 0 from the start, G gives 0 there, and then every quantity below stays at its neutral
+            // value by arithmetic alone (ds = 0, dlam = -0, products 0); only the centring term needs its two masks.  The
+            // reciprocal of lam = 0 is a NaN that the running maximum drops.  (64 double selects per iteration less.)
+            for (int c = 0; c < 8; ++c) { rc[c] = s[c] * lam[c]; dsa[c] = 0.0; dla[c] = 0.0; }
 #pragma unroll
             for (int ph = 0; ph < 2; ++ph) {
                 double ha, hd;
@@ -928,9 +933,9 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                 double tmax = 0.0;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
-                    dsa[c] = mk[c] ? -rp[c] - g[c] : 0.0;
-                    dla[c] = mk[c] ? -(rc[c] + lam[c] * dsa[c]) * sinv[c] : 0.0;   // rc = s lam in the predictor: -lam - w ds
-                    const double linv = mk[c] ? rcp(lam[c]) : 0.0;
+                    dsa[c] = -rp[c] - g[c];
+                    dla[c] = -(rc[c] + lam[c] * dsa[c]) * sinv[c];                 // rc = s lam in the predictor: -lam - w ds
+                    const double linv = rcp(lam[c]);
                     tmax = dmax_run(dmax_run(tmax, -dsa[c] * sinv[c]), -dla[c] * linv);
                 }
                 tmax = warp_max_nn(tmax);
@@ -942,8 +947,9 @@ __device__ __forceinline__ int mpc_step_body(const StepParams& p, const int b) {
                     const double mu_aff = warp_sum(sl) / m_cnt;
                     const double r = mu_aff / mu;
                     const double sigma_mu = r * r * r * mu;
+                    const double sig_a = mk[0] ? sigma_mu : 0.0, sig_r = mk[4] ? sigma_mu : 0.0;
 #pragma unroll
-                    for (int c = 0; c < 8; ++c) rc[c] = mk[c] ? s[c] * lam[c] + dsa[c] * dla[c] - sigma_mu : 0.0;
+                    for (int c = 0; c < 8; ++c) rc[c] = s[c] * lam[c] + dsa[c] * dla[c] - ((c == 4 || c == 5) ? sig_r : sig_a);
                 } else {
                     // Fraction to the boundary: 0.99 while the gap is large, -> 1 as it closes (Mehrotra's adaptive rule).  With a
                     // fixed 0.99 every residual and the gap shrink by exactly 100x per iteration in the end game (linear); with
