@@ -43,6 +43,7 @@ for T in (10, 13, 20, 40, 80):
             ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
             it_acc = torch.zeros((), dtype=torch.float64, device=dev)
             bad = torch.zeros((), dtype=torch.int64, device=dev)
+            exc = torch.zeros((), dtype=torch.int64, device=dev)     # status 3: the reference's nearest-index Exception, not a failed solve
             with torch.cuda.stream(stream):
                 for _ in range(LEAD):
                     ses.closed_loop_dev(1, 0, stream.cuda_stream, goal_test=False)
@@ -52,12 +53,14 @@ for T in (10, 13, 20, 40, 80):
                     ses.closed_loop_dev(1, 0, stream.cuda_stream, goal_test=False)
                     ev[k][1].record(stream)
                     it_acc += iters_v.double().mean()
-                    bad += (status_v >= 2).sum()
+                    bad += (status_v == 2).sum()
+                    exc += (status_v == 3).sum()
             torch.cuda.synchronize(dev)
             ms = np.array([a.elapsed_time(b) for a, b in ev])
             rows.append(dict(T=T, B=B, L=L, steps=steps, ms_mean=float(ms.mean()), ms_p50=float(np.percentile(ms, 50)),
                              ms_p99=float(np.percentile(ms, 99)), solves_per_s=float(B * steps / ms.sum() * 1e3),
-                             mean_ipm_iters=float(it_acc.item()) / steps, failed_solves=int(bad.item())))
+                             mean_ipm_iters=float(it_acc.item()) / steps, failed_solves=int(bad.item()),
+                             nearest_index_exceptions=int(exc.item())))
             print(rows[-1], flush=True)
     ses.close()
 
