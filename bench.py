@@ -264,6 +264,7 @@ def run_b200(args):
     nc_v = torch.as_tensor(ses.device_view("ncourse"), device=dev)
     status_v = torch.as_tensor(ses.device_view("status"), device=dev)
     bad_acc = torch.zeros((), dtype=torch.int64, device=dev)
+    exc_acc = torch.zeros((), dtype=torch.int64, device=dev)      # status 3: the reference's nearest-index Exception, not a failed solve
     l0 = ses.launches
     lead_launches = 0
     t_wall0 = time.perf_counter()
@@ -278,7 +279,8 @@ def run_b200(args):
             ses.closed_loop_dev(1, 0, sptr, goal_test=False)
             ev[k][1].record(stream)
             iters_acc += iters_v
-            bad_acc += (status_v >= 2).sum()
+            bad_acc += (status_v == 2).sum()
+            exc_acc += (status_v == 3).sum()
     barrier()
     t_wall1 = time.perf_counter()
     launches = ses.launches - l0 - lead_launches
@@ -292,6 +294,7 @@ def run_b200(args):
     k_mean = float(iters_acc.double().mean().item()) / max(args.steps, 1)
     scan_mean = float(scan_acc.double().mean().item()) / max(args.steps, 1)
     n_bad = int(bad_acc.item())
+    n_exc = int(exc_acc.item())
 
     # ---- end to end through the host-buffer C ABI, same control steps ------------------------------------------------
     L = cfg.wheelbase
@@ -338,7 +341,7 @@ def run_b200(args):
                        "batch_per_gpu": B, "horizon": T, "seed": args.seed, "sharding": f"scenarios x{world}",
                        "l2": "flushed between timed steps (256 MiB memset outside the event pairs)",
                        "mean_ipm_iters": k_mean, "ipm_iterations_per_sec": value * k_mean,
-                       "mean_course_points_scanned": scan_mean, "failed_solves": n_bad},
+                       "mean_course_points_scanned": scan_mean, "failed_solves": n_bad, "nearest_index_exceptions": n_exc},
             "cvxpy_ecos_present": probe_cvxpy_ecos(),
             "clocks": clocks,
             "e2e": {"value": B * world * args.steps / e2e_s_max, "unit": UNIT,
@@ -452,6 +455,7 @@ def run_sweep(args):
                        "l2": "inputs larger than L2 (65536 resident problems x 25.6 KB of per-problem state)"},
             "clocks": clocks,
             "sweep": {"solves": total, "reached_goal": int(full["reached_goal"].sum().item()), "failed_solves": int(full["fail_count"].sum().item()),
+                      "failed_solves_counts": "status >= 2: failed solves and nearest-index Exceptions of the reference (scripts/triage_sweep_failures.py tells them apart)",
                       "workload_gen_s_untimed": gen_s, "closed_loops_ms_device_max_over_ranks": loop_ms,
                       "wall_s_loops": t_loop - t0, "wall_s_gather": t_gather - t_loop, "wall_s_d2h_rank0": t_end - t_gather,
                       "wall_s_total": t_end - t0, "gather_ms": gather_ms, "gathered_bytes": gathered_bytes,
